@@ -1,0 +1,538 @@
+"""oracle/vcm_ref.py -- TEST INFRASTRUCTURE ONLY (the checker, never the product).
+
+numpy restatement of the array arithmetic of the reference's coarse-graining path.
+Paths are relative to /root/reference/external/vcm/vcm/ unless noted.  xarray, dask
+and xgcm are not installed in this image, so the labelled-array layer is dropped
+and every function works on plain ndarrays with the horizontal axes LAST
+(``[..., y, x]``) and, where a vertical axis exists, ``[..., z, y, x]`` -- the layout
+of FV3 restart files (tests/_coarsen_restarts_regression_tests/schemas/*.json).
+
+Third-party arithmetic restated here because it is not under /root/reference:
+  * xarray 0.19.0 ``Coarsen.sum`` = reshape into windows + ``nansum`` (NaN replaced by
+    0, then ``np.sum``) -- call sites cubedsphere/coarsen.py:211-212,260-261,839-840;
+  * xarray ``Variable.cumsum`` = ``nancumsum`` -- calc/thermo/vertically_dependent.py:63;
+  * xgcm 0.6.1 ``Grid.interp`` centre->outer with FV3_FACE_CONNECTIONS
+    (cubedsphere/xgcm.py:7-34; call sites cubedsphere/regridz.py:126,
+    cubedsphere/coarsen_restarts.py:847).
+Pinned by the golden vectors in tests/golden/ (made by tests/golden/make_golden.py
+from the reference's own regression JSONs) and the inline known answers of the
+reference's unit tests (tests/test_oracle.py).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs may import this module.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+def build(force=False):
+    """Compile oracle/liboracle.so (gcc, -O2 -ffp-contract=off) if missing."""
+    so = os.path.join(_HERE, "liboracle.so")
+    srcs = [os.path.join(_HERE, s) for s in ("mappm_ref.c", "blocksum_ref.c")]
+    stale = (not os.path.exists(so)) or any(
+        os.path.getmtime(s) > os.path.getmtime(so) for s in srcs
+    )
+    if force or stale:
+        subprocess.check_call(["make", "-C", _HERE, "-B", "liboracle.so"], stdout=subprocess.DEVNULL)
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = ctypes.CDLL(build())
+        fp = ctypes.POINTER(ctypes.c_float)
+        dp = ctypes.POINTER(ctypes.c_double)
+        _LIB.mappm_ref.argtypes = [ctypes.c_int, ctypes.c_int, fp, fp, ctypes.c_int, fp, fp,
+                                   ctypes.c_int, ctypes.c_int, ctypes.c_int]
+        _LIB.mappm_ref.restype = ctypes.c_int
+        _LIB.mappm_profile_ref.argtypes = [ctypes.c_int, ctypes.c_int, fp, fp, fp, fp, fp,
+                                           ctypes.c_int, ctypes.c_int]
+        _LIB.mappm_profile_ref.restype = ctypes.c_int
+        _LIB.blocksum_ordered_f32.argtypes = [fp, ctypes.c_long] + [ctypes.c_int] * 4 + [fp]
+        _LIB.blocksum_ordered_f64.argtypes = [dp, ctypes.c_long] + [ctypes.c_int] * 4 + [dp]
+    return _LIB
+
+
+def _fptr(a):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_float))
+
+
+# --------------------------------------------------------------------------------------
+# mappm  (external/mappm/mappm/mappm.f90:10; Python-visible f2py signature used at
+# cubedsphere/regridz.py:332-334)
+# --------------------------------------------------------------------------------------
+def mappm(pe1, q1, pe2, i1=1, i2=None, iv=1, kord=1, ptop=0.0, nthreads=1):
+    """q2[ncol,kn] float32.  f2py casts every input to float32 and coerces the scalar
+    arguments with int() (external/vcm/tests/test_mappm.py:9-13 passes floats)."""
+    pe1 = np.ascontiguousarray(pe1, dtype=np.float32)
+    q1 = np.ascontiguousarray(q1, dtype=np.float32)
+    pe2 = np.ascontiguousarray(pe2, dtype=np.float32)
+    ncol, km1 = pe1.shape
+    km, kn = km1 - 1, pe2.shape[1] - 1
+    assert q1.shape == (ncol, km) and pe2.shape[0] == ncol
+    q2 = np.empty((ncol, kn), dtype=np.float32)
+    rc = lib().mappm_ref(ncol, km, _fptr(pe1), _fptr(q1), kn, _fptr(pe2), _fptr(q2),
+                         int(iv), int(kord), int(nthreads))
+    if rc != 0:
+        raise ValueError(f"mappm_ref: unsupported km={km} for kord={kord}")
+    return q2
+
+
+def mappm_profile(pe1, q1, iv=1, kord=1):
+    pe1 = np.ascontiguousarray(pe1, dtype=np.float32)
+    q1 = np.ascontiguousarray(q1, dtype=np.float32)
+    ncol, km = q1.shape
+    out = [np.empty((ncol, km), dtype=np.float32) for _ in range(3)]
+    rc = lib().mappm_profile_ref(ncol, km, _fptr(pe1), _fptr(q1), *[_fptr(o) for o in out],
+                                 int(iv), int(kord))
+    if rc != 0:
+        raise ValueError("mappm_profile_ref failed")
+    return out
+
+
+def blocksum_ordered(a, fy, fx):
+    """Explicit-order window sum (oracle/blocksum_ref.c); a is [..., ny, nx]."""
+    a = np.ascontiguousarray(a)
+    ny, nx = a.shape[-2:]
+    out = np.empty(a.shape[:-2] + (ny // fy, nx // fx), dtype=a.dtype)
+    nb = int(np.prod(a.shape[:-2], dtype=np.int64))
+    if a.dtype == np.float32:
+        lib().blocksum_ordered_f32(_fptr(a), nb, ny, nx, fy, fx, _fptr(out))
+    elif a.dtype == np.float64:
+        dp = ctypes.POINTER(ctypes.c_double)
+        lib().blocksum_ordered_f64(a.ctypes.data_as(dp), nb, ny, nx, fy, fx, out.ctypes.data_as(dp))
+    else:
+        raise TypeError(a.dtype)
+    return out
+
+
+# --------------------------------------------------------------------------------------
+# xarray coarsen().sum() and friends
+# --------------------------------------------------------------------------------------
+def coarsen_sum(a, fy, fx):
+    """xarray 0.19 ``a.coarsen({y: fy, x: fx}).sum()`` on the last two axes:
+    windows by reshape, NaN -> 0 (skipna default for floats), np.sum over the window
+    axes.  fy or fx may be 1 (1-D coarsening as in coarsen.py:259-261)."""
+    a = np.ascontiguousarray(a)
+    ny, nx = a.shape[-2:]
+    if ny % fy or nx % fx:
+        raise ValueError("window does not divide the dimension (xarray boundary='exact')")
+    r = a.reshape(a.shape[:-2] + (ny // fy, fy, nx // fx, fx))
+    if np.issubdtype(r.dtype, np.floating):
+        r = np.where(np.isnan(r), np.zeros((), dtype=r.dtype), r)
+    return np.sum(r, axis=(-3, -1))
+
+
+def coarsen_reduce(a, fy, fx, method):
+    """xarray ``coarsen(...).<method>()`` for min/max/mean/sum (coarsen.py:838-840).
+    NaN-skipping like xarray's defaults."""
+    if method == "sum":
+        return coarsen_sum(a, fy, fx)
+    a = np.ascontiguousarray(a)
+    ny, nx = a.shape[-2:]
+    r = a.reshape(a.shape[:-2] + (ny // fy, fy, nx // fx, fx))
+    fn = {"min": np.nanmin, "max": np.nanmax, "mean": np.nanmean, "median": np.nanmedian}[method]
+    isfloat = np.issubdtype(r.dtype, np.floating)
+    if not isfloat:
+        fn = {"min": np.min, "max": np.max, "mean": np.mean, "median": np.median}[method]
+    with np.errstate(all="ignore"):
+        import warnings
+
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            return fn(r, axis=(-3, -1))
+
+
+def weighted_block_average(obj, weights, f):
+    """cubedsphere/coarsen.py:183-218: nansum(obj*w)/nansum(w) over f x f windows of
+    the last two axes.  ``weights`` broadcasts against ``obj`` from the right after
+    optional leading-axis alignment by the caller (xarray aligns by name; here the
+    caller passes arrays that numpy-broadcast, e.g. area[tile,1,1,y,x])."""
+    prod = obj * weights
+    num = coarsen_sum(prod, f, f)
+    den = coarsen_sum(weights, f, f)
+    with np.errstate(all="ignore"):
+        return num / den
+
+
+def edge_weighted_block_average(obj, spacing, f, edge="x"):
+    """cubedsphere/coarsen.py:221-273 on [..., y, x] arrays: edge='x' sums along x and
+    keeps every f-th y line; edge='y' the converse."""
+    prod = spacing * obj
+    if edge == "x":
+        num, den = coarsen_sum(prod, 1, f), coarsen_sum(spacing, 1, f)
+        with np.errstate(all="ignore"):
+            res = num / den
+        return res[..., ::f, :]
+    elif edge == "y":
+        num, den = coarsen_sum(prod, f, 1), coarsen_sum(spacing, f, 1)
+        with np.errstate(all="ignore"):
+            res = num / den
+        return res[..., :, ::f]
+    raise ValueError(f"'edge' most be either 'x' or 'y'; got {edge}.")
+
+
+def block_edge_coarsen(obj, f, edge="x", method="sum"):
+    """cubedsphere/coarsen.py:629-683."""
+    if edge == "x":
+        return coarsen_reduce(obj, 1, f, method)[..., ::f, :]
+    elif edge == "y":
+        return coarsen_reduce(obj, f, 1, method)[..., :, ::f]
+    raise ValueError(f"'edge' most be either 'x' or 'y'; got {edge}.")
+
+
+def block_reduce(image, block_size, func=np.sum, cval=0):
+    """Restatement of cubedsphere/_skimage.py:125-202 (pad trailing edges with cval,
+    block view, func over the block axes)."""
+    image = np.asarray(image)
+    if len(block_size) != image.ndim:
+        raise ValueError("`block_size` must have the same length as `image.shape`.")
+    pad_width = []
+    for n, b in zip(image.shape, block_size):
+        if b < 1:
+            raise ValueError("Down-sampling factors must be >= 1.")
+        pad_width.append((0, (b - n % b) % b))
+    image = np.pad(image, pad_width=pad_width, mode="constant", constant_values=cval)
+    shp = []
+    for n, b in zip(image.shape, block_size):
+        shp += [n // b, b]
+    blocked = image.reshape(shp)
+    # block view has all coarse axes first, then the block axes
+    nd = image.ndim
+    blocked = blocked.transpose([2 * i for i in range(nd)] + [2 * i + 1 for i in range(nd)])
+    return func(blocked, axis=tuple(range(nd, 2 * nd)))
+
+
+def horizontal_block_reduce(obj, f, func, cval=np.nan):
+    """cubedsphere/coarsen.py:520-554 on the last two axes."""
+    bs = (1,) * (obj.ndim - 2) + (f, f)
+    return block_reduce(obj, bs, func, cval)
+
+
+def mode_reduce(arr, axis, nan_policy="propagate"):
+    """cubedsphere/coarsen.py:686-747 (_mode/_ureduce/_mode_reduce): scipy.stats.mode
+    over a tuple of axes; ties -> smallest value."""
+    import scipy.stats
+
+    arr = np.asanyarray(arr)
+    nd = arr.ndim
+    keep = sorted(set(range(nd)) - set(axis))
+    arr = np.moveaxis(arr, keep, range(len(keep)))
+    arr = arr.reshape(arr.shape[: len(keep)] + (-1,))
+    res = scipy.stats.mode(arr, axis=-1, nan_policy=nan_policy, keepdims=True).mode
+    return np.squeeze(np.asarray(res), -1)
+
+
+def repeat_staggered(a, f, axis):
+    """cubedsphere/coarsen.py:843-866: odd-size axis = interfaces, last not repeated."""
+    n = a.shape[axis]
+    if n % 2 == 1:
+        sl = [slice(None)] * a.ndim
+        sl[axis] = slice(None, -1)
+        sl2 = [slice(None)] * a.ndim
+        sl2[axis] = slice(-1, None)
+        return np.concatenate([np.repeat(a[tuple(sl)], f, axis=axis), a[tuple(sl2)]], axis=axis)
+    return np.repeat(a, f, axis=axis)
+
+
+def block_upsample(a, f, axes=(-2, -1)):
+    """cubedsphere/coarsen.py:869-897."""
+    for ax in axes:
+        a = repeat_staggered(a, f, ax)
+    return a
+
+
+def block_upsample_like(a, ref_shape_yx):
+    """cubedsphere/coarsen.py:900-938: factor inferred from the x axis."""
+    nx_c, nx_f = a.shape[-1], ref_shape_yx[1]
+    f = (nx_f - 1) // (nx_c - 1) if nx_c % 2 == 1 else nx_f // nx_c
+    return block_upsample(a, f, (-1, -2))
+
+
+def coarsen_coords(coord, f):
+    """cubedsphere/coarsen.py:83-132: ((c[::f]-1)//f+1) as float32."""
+    c = np.asarray(coord)
+    return ((c[::f] - 1) // f + 1).astype(int).astype(np.float32)
+
+
+# --------------------------------------------------------------------------------------
+# pressure helpers (calc/thermo/vertically_dependent.py)
+# --------------------------------------------------------------------------------------
+def pressure_at_interface(delp, toa_pressure=300.0, z_axis=-3):
+    """:41-66 -- concat(top, delp) then nancumsum along z, in delp's dtype."""
+    delp = np.asarray(delp)
+    top_shape = list(delp.shape)
+    top_shape[z_axis] = 1
+    top = np.full(top_shape, toa_pressure, dtype=delp.dtype)
+    return np.nancumsum(np.concatenate([top, delp], axis=z_axis), axis=z_axis)
+
+
+def pressure_at_midpoint_log(delp, toa_pressure=300.0, z_axis=-3):
+    """:153-179 -- delp / diff(log(p_interface))."""
+    pi = pressure_at_interface(delp, toa_pressure, z_axis)
+    with np.errstate(all="ignore"):
+        dlogp = np.diff(np.log(pi), axis=z_axis)
+        return delp / dlogp
+
+
+def surface_pressure_from_delp(delp, p_toa=300.0, z_axis=-3):
+    """:189-208 -- NaN-skipping sum + p_toa."""
+    return np.nansum(delp, axis=z_axis) + p_toa
+
+
+# --------------------------------------------------------------------------------------
+# vertical regridding (cubedsphere/regridz.py)
+# --------------------------------------------------------------------------------------
+def regrid_vertical(p_in, f_in, p_out, iv=1, kord=1, z_axis=-3, nthreads=1):
+    """:223-338 -- columns flattened z-last, mappm (fp32), shape/dim order restored."""
+    if p_in.shape[z_axis] - 1 != f_in.shape[z_axis]:
+        raise ValueError("f_in must have a vertical dimension one shorter than p_in")
+    pz = np.moveaxis(p_in, z_axis, -1)
+    fz = np.moveaxis(f_in, z_axis, -1)
+    oz = np.moveaxis(p_out, z_axis, -1)
+    if pz.shape[:-1] != fz.shape[:-1] or pz.shape[:-1] != oz.shape[:-1]:
+        raise ValueError("All dimensions except vertical must be same size for p_in, f_in and p_out")
+    q2 = mappm(pz.reshape(-1, pz.shape[-1]), fz.reshape(-1, fz.shape[-1]),
+               oz.reshape(-1, oz.shape[-1]), 1, None, iv, kord, 0.0, nthreads=nthreads)
+    return np.moveaxis(q2.reshape(oz.shape[:-1] + (oz.shape[-1] - 1,)), -1, z_axis)
+
+
+def mask_weights(weights, pfull_coarse_on_fine, phalf_coarse_on_fine, phalf_fine,
+                 extrapolate=False, z_axis=-3):
+    """:200-220.  ``weights`` must broadcast against [..., z, y, x].  The result keeps
+    the weights' dtype (xarray ``where(cond, other=0.0)`` with a Python scalar)."""
+    surf = np.take(phalf_fine, [-1], axis=z_axis)
+    if extrapolate:
+        cond = pfull_coarse_on_fine < surf
+    else:
+        sl = [slice(None)] * phalf_coarse_on_fine.ndim
+        sl[z_axis] = slice(1, None)
+        cond = phalf_coarse_on_fine[tuple(sl)] < surf
+    w = np.broadcast_to(weights, cond.shape)
+    return np.where(cond, w, np.zeros((), dtype=w.dtype))
+
+
+def _regrid_given_delp(fields, delp_fine, delp_coarse, weights, toa_pressure, extrapolate=False,
+                       iv=1, kord=1, nthreads=1):
+    """:149-197.  fields: dict name -> [..., z, y, x]; weights [..., 1, y, x]-broadcastable."""
+    delp_c_up = block_upsample_like(delp_coarse, delp_fine.shape[-2:])
+    phalf_c_up = pressure_at_interface(delp_c_up, toa_pressure)
+    phalf_fine = pressure_at_interface(delp_fine, toa_pressure)
+    out = {}
+    for name, f in fields.items():
+        out[name] = regrid_vertical(phalf_fine, f, phalf_c_up, iv=iv, kord=kord, nthreads=nthreads)
+    pfull_c_up = pressure_at_midpoint_log(delp_c_up, toa_pressure)
+    masked = mask_weights(weights, pfull_c_up, phalf_c_up, phalf_fine, extrapolate=extrapolate)
+    return out, masked
+
+
+def regrid_to_area_weighted_pressure(fields, delp, area, toa_pressure, f, extrapolate=False,
+                                     nthreads=1):
+    """:31-78.  area must broadcast to delp ([tile,1,1,y,x] for [tile,Time,z,y,x])."""
+    delp_coarse = weighted_block_average(delp, area, f)
+    return _regrid_given_delp(fields, delp, delp_coarse, area, toa_pressure, extrapolate,
+                              nthreads=nthreads)
+
+
+# xgcm face connections, cubedsphere/xgcm.py:7-34: tile -> axis -> (left, right), each
+# (neighbour tile, neighbour axis)
+FV3_FACE_CONNECTIONS = {
+    0: {"x": ((4, "y"), (1, "x")), "y": ((5, "y"), (2, "x"))},
+    1: {"x": ((0, "x"), (3, "y")), "y": ((5, "x"), (2, "y"))},
+    2: {"x": ((0, "y"), (3, "x")), "y": ((1, "y"), (4, "x"))},
+    3: {"x": ((2, "x"), (5, "y")), "y": ((1, "x"), (4, "y"))},
+    4: {"x": ((2, "y"), (5, "x")), "y": ((3, "y"), (0, "x"))},
+    5: {"x": ((4, "x"), (1, "y")), "y": ((3, "x"), (0, "y"))},
+}
+
+
+def _edge_line(tile_arr, axis, last):
+    """Boundary line of a [..., y, x] tile: along 'x' -> the first/last column (indexed
+    by y); along 'y' -> the first/last row (indexed by x)."""
+    idx = -1 if last else 0
+    return tile_arr[..., :, idx] if axis == "x" else tile_arr[..., idx, :]
+
+
+def stagger_delp(delp, axis):
+    """xgcm ``grid.interp(delp, axis)`` centre -> outer for 6 tiles on axis 0
+    (regridz.py:118-132).  out[j] = 0.5*(ext[j-1]+ext[j]); ghosts come from the
+    neighbour tiles: left ghost = neighbour's LAST line along its connecting axis,
+    right ghost = its FIRST line; reversed when the neighbour's axis differs."""
+    assert delp.shape[0] == 6
+    outs = []
+    for t in range(6):
+        (lt, lax), (rt, rax) = FV3_FACE_CONNECTIONS[t][axis]
+        left = _edge_line(delp[lt], lax, last=True)
+        right = _edge_line(delp[rt], rax, last=False)
+        if lax != axis:
+            left = left[..., ::-1]
+        if rax != axis:
+            right = right[..., ::-1]
+        if axis == "x":
+            ext = np.concatenate([left[..., :, None], delp[t], right[..., :, None]], axis=-1)
+            outs.append(0.5 * (ext[..., :, :-1] + ext[..., :, 1:]))
+        else:
+            ext = np.concatenate([left[..., None, :], delp[t], right[..., None, :]], axis=-2)
+            outs.append(0.5 * (ext[..., :-1, :] + ext[..., 1:, :]))
+    return np.stack(outs, axis=0)
+
+
+def regrid_to_edge_weighted_pressure(fields, delp, length, toa_pressure, f, edge="x",
+                                     extrapolate=False, nthreads=1):
+    """:81-146.  edge='x' (u, dx on y-interfaces) staggers delp along y."""
+    interp_axis = "x" if edge == "y" else "y"
+    delp_stag = stagger_delp(delp, interp_axis)
+    delp_stag_coarse = edge_weighted_block_average(delp_stag, length, f, edge=edge)
+    return _regrid_given_delp(fields, delp_stag, delp_stag_coarse, length, toa_pressure,
+                              extrapolate, nthreads=nthreads)
+
+
+# --------------------------------------------------------------------------------------
+# restart recipes (cubedsphere/coarsen_restarts.py).  ds: dict name -> array laid out
+# [tile, Time, z, y, x] (3-D) or [tile, Time, y, x] (2-D); area/dx/dy: [tile, y, x].
+# --------------------------------------------------------------------------------------
+def _w5(w):  # [tile,y,x] -> [tile,1,1,y,x]
+    return w[:, None, None, :, :]
+
+
+def _w4(w):  # [tile,y,x] -> [tile,1,y,x]
+    return w[:, None, :, :]
+
+
+def _wfor(a, w):
+    return _w5(w) if a.ndim == 5 else _w4(w)
+
+
+def coarse_grain_fv_core(ds, delp, area, dx, dy, f, coarsen_agrid_winds=False, mass_weighted=True):
+    """:335-427."""
+    if mass_weighted:
+        area_vars, mass_vars = ["phis", "delp", "DZ"], ["W", "T"]
+    else:
+        area_vars, mass_vars = ["phis", "delp", "DZ", "W", "T"], []
+    if coarsen_agrid_winds:
+        if not ("ua" in ds and "va" in ds):
+            raise ValueError("If 'coarsen_agrid_winds' is active, 'ua' and 'va' "
+                             "must be present in the 'fv_core.res' restart files.")
+        (mass_vars if mass_weighted else area_vars).extend(["ua", "va"])
+    out = {}
+    for v in area_vars:
+        out[v] = weighted_block_average(ds[v], _wfor(ds[v], area), f)
+    mass = delp * _w5(area)
+    for v in mass_vars:
+        out[v] = weighted_block_average(ds[v], mass, f)
+    out["u"] = edge_weighted_block_average(ds["u"], _w5(dx), f, edge="x")
+    out["v"] = edge_weighted_block_average(ds["v"], _w5(dy), f, edge="y")
+    return out
+
+
+def coarse_grain_fv_core_on_pressure(ds, delp, area, dx, dy, toa_pressure, f,
+                                     coarsen_agrid_winds=False, extrapolate=False, nthreads=1):
+    """:430-556."""
+    area_vars, masked_vars = ["phis", "delp", "DZ"], ["W", "T"]
+    if coarsen_agrid_winds:
+        if not ("ua" in ds and "va" in ds):
+            raise ValueError("If 'coarsen_agrid_winds' is active, 'ua' and 'va' "
+                             "must be present in the 'fv_core.res' restart files.")
+        masked_vars.extend(["ua", "va"])
+    reg, masked_area = regrid_to_area_weighted_pressure(
+        {v: ds[v] for v in masked_vars}, delp, _w5(area), toa_pressure, f, extrapolate, nthreads)
+    reg_u, masked_dx = regrid_to_edge_weighted_pressure(
+        {"u": ds["u"]}, delp, _w5(dx), toa_pressure, f, "x", extrapolate, nthreads)
+    reg_v, masked_dy = regrid_to_edge_weighted_pressure(
+        {"v": ds["v"]}, delp, _w5(dy), toa_pressure, f, "y", extrapolate, nthreads)
+    out = {}
+    for v in area_vars:
+        out[v] = weighted_block_average(ds[v], _wfor(ds[v], area), f)
+    for v in masked_vars:
+        out[v] = weighted_block_average(reg[v], masked_area, f)
+    out["u"] = edge_weighted_block_average(reg_u["u"], masked_dx, f, edge="x")
+    out["v"] = edge_weighted_block_average(reg_v["v"], masked_dy, f, edge="y")
+    return out
+
+
+FRACTION_TRACERS = ["cld_amt"]
+NON_FRACTION_TRACERS = ["sphum", "liq_wat", "rainwat", "ice_wat", "snowwat", "graupel", "o3mr",
+                        "sgs_tke"]
+
+
+def coarse_grain_fv_tracer(ds, delp, area, f, mass_weighted=True):
+    """:856-900."""
+    if mass_weighted:
+        area_vars, mass_vars = FRACTION_TRACERS, NON_FRACTION_TRACERS
+    else:
+        area_vars, mass_vars = FRACTION_TRACERS + NON_FRACTION_TRACERS, []
+    out = {}
+    for v in area_vars:
+        out[v] = weighted_block_average(ds[v], _w5(area), f)
+    mass = delp * _w5(area)
+    for v in mass_vars:
+        out[v] = weighted_block_average(ds[v], mass, f)
+    return out
+
+
+def coarse_grain_fv_tracer_on_pressure(ds, delp, area, toa_pressure, f, extrapolate=False,
+                                       nthreads=1):
+    """:903-961."""
+    reg, masked_area = regrid_to_area_weighted_pressure(ds, delp, _w5(area), toa_pressure, f,
+                                                        extrapolate, nthreads)
+    return {v: weighted_block_average(reg[v], masked_area, f) for v in ds}
+
+
+def coarse_grain_fv_srf_wnd(ds, area, f):
+    """:964-987."""
+    return {v: weighted_block_average(ds[v], _w4(area), f) for v in ("u_srf", "v_srf")}
+
+
+# --------------------------------------------------------------------------------------
+# fine_res_budget variant (workflows/fine_res_budget/budget/budgets.py:49-77)
+# --------------------------------------------------------------------------------------
+def pressure_level_average(delp_fine, delp_coarse, area, field, f, nthreads=1):
+    """budgets.py:49-57: interfaces of the COARSE delp upsampled, remap, UNMASKED
+    area-weighted block average.  [..., z, y, x] arrays; area broadcastable."""
+    pi = pressure_at_interface(delp_fine)
+    pi_c_up = block_upsample(pressure_at_interface(delp_coarse), f, (-1, -2))
+    fg = regrid_vertical(pi, field, pi_c_up, nthreads=nthreads)
+    return weighted_block_average(fg, area, f)
+
+
+def area_above_fine_surface(delp_fine, delp_coarse, area, f):
+    """budgets.py:62-77."""
+    pressure_c_up = block_upsample(pressure_at_midpoint_log(delp_coarse), f, (-1, -2))
+    ps = surface_pressure_from_delp(delp_fine)
+    ps = np.expand_dims(ps, -3)
+    w = np.where(pressure_c_up <= ps, np.broadcast_to(area, pressure_c_up.shape),
+                 np.zeros((), dtype=np.asarray(area).dtype))
+    return coarsen_sum(w, f, f)
+
+
+# --------------------------------------------------------------------------------------
+# synthetic inputs of the reference regression test
+# (external/synth/synth/core.py:59-67,136; external/vcm/tests/test_coarsen_restarts.py:24-30)
+# --------------------------------------------------------------------------------------
+def synth_array(shape, dtype, lo=-1000.0, hi=1000.0):
+    np.random.seed(0)
+    return np.random.uniform(low=lo, high=hi, size=shape).astype(dtype)
+
+
+def regression_inputs():
+    """Regenerates the C4 (6 tiles, 7 levels) inputs of test_coarsen_restarts.py."""
+    f8, f4 = np.float64, np.float32
+    core = {
+        "u": synth_array((6, 1, 7, 5, 4), f8), "v": synth_array((6, 1, 7, 4, 5), f8),
+        "W": synth_array((6, 1, 7, 4, 4), f8), "DZ": synth_array((6, 1, 7, 4, 4), f8),
+        "T": synth_array((6, 1, 7, 4, 4), f8), "delp": synth_array((6, 1, 7, 4, 4), f8, 3, 5),
+        "phis": synth_array((6, 1, 4, 4), f8), "ua": synth_array((6, 1, 7, 4, 4), f8),
+        "va": synth_array((6, 1, 7, 4, 4), f8),
+    }
+    tracer = {n: synth_array((6, 1, 7, 4, 4), f8) for n in NON_FRACTION_TRACERS + FRACTION_TRACERS}
+    srf = {"u_srf": synth_array((6, 1, 4, 4), f8), "v_srf": synth_array((6, 1, 4, 4), f8)}
+    grid = {"area": synth_array((6, 4, 4), f4, 0.5, 1), "dx": synth_array((6, 5, 4), f4, 0.5, 1),
+            "dy": synth_array((6, 4, 5), f4, 0.5, 1)}
+    return core, tracer, srf, grid
