@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""bench.py -- C384->C48 pressure-level coarse-graining throughput on B200.
+
+Workload (BASELINE.json metric, configs[2]): the A-grid part of
+`_coarse_grain_fv_core_on_pressure` with coarsen_agrid_winds=True -- delp + N=4 fields
+(W, T, ua, va), 6 tiles x 79 levels x 384 x 384 fp32, factor 8, extrapolate=False, kord=1, iv=1:
+coarse delp -> interface pressures -> PPM remap of each field onto the coarse pressure levels ->
+below-surface mask -> masked block average, ONE fused kernel launch per step.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--mode exact|fast] [--impl reference]
+
+N>1 (under torchrun): weak scaling, every rank coarsens its own synthetic timestep (the
+reference's Beam pipeline fans out over timesteps the same way), then an NCCL all-gather collects
+the small coarse outputs; time = max over ranks.
+
+Prints ONE JSON line.  `value` = fine grid points/s over all ranks with inputs resident in HBM;
+`e2e` = the same through the public API from pinned HOST buffers (H2D + kernel + D2H per step);
+`roofline` = algorithmic bytes / CUDA-event time of the fused kernel vs the measured HBM copy
+bandwidth (MEASURED_PEAKS.json); `cpu_baseline` = the CPU oracle (numpy + C mappm restatement,
+all host cores) on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NTILE, KM, NFINE, FACTOR, NFIELDS = 6, 79, 384, 8, 4
+TOA = 300.0
+METRIC = "fine grid pts/s, C384->C48 pressure-level coarsening (delp + 4 fields, 6 tiles x 79 levels)"
+UNIT = "fine grid points/s"
+FALLBACK_HBM_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md fallback
+
+
+def algorithmic_bytes(ntile=NTILE, km=KM, n=NFINE, f=FACTOR, nf=NFIELDS, elt=4):
+    """delp + nf fields + 2-D weights read once, coarse fields + coarse delp written
+    once = 4*km*(nf+1)+4 B per fine column + outputs (1608.7 B/col at km=79, nf=4)."""
+    cols = ntile * n * n
+    read = cols * (elt * km * (nf + 1) + elt)
+    write = ntile * km * (n // f) ** 2 * elt * (nf + 1)
+    return read + write
+
+
+def points_per_step(ntile=NTILE, km=KM, n=NFINE, nf=NFIELDS):
+    return ntile * km * n * n * nf
+
+
+def synth_numpy(seed, ntile=NTILE, km=KM, ny=NFINE, nx=NFINE):
+    """Seeded synthetic inputs of SURVEY.md 8d (numpy, used for the CPU sample)."""
+    rng = np.random.default_rng(seed)
+    yy, xx = np.meshgrid(np.linspace(0, 6, ny), np.linspace(0, 6, nx), indexing="ij")
+    ps = 8.6e4 + 1.4e4 * np.sin(yy * 1.3)[None] * np.cos(xx * 1.1)[None] + rng.normal(0, 1500, size=(ntile, ny, nx))
+    ps = np.clip(ps, 5.0e4, 1.04e5)
+    b = np.diff(np.linspace(0, 1, km + 1) ** 1.6)
+    delp = ((ps[:, None] - TOA) * b[None, :, None, None] * (1 + rng.uniform(-0.02, 0.02, size=(ntile, km, ny, nx)))).astype(np.float32)
+    area = (rng.uniform(3.6e8, 8.3e8, size=(ntile, ny, nx))).astype(np.float32)
+    fields = [rng.uniform(180, 320, size=(ntile, km, ny, nx)).astype(np.float32)] + \
+             [rng.normal(0, 10, size=(ntile, km, ny, nx)).astype(np.float32) for _ in range(NFIELDS - 1)]
+    return delp, area, fields
+
+
+def synth_device(torch, seed, dev):
+    """Same distribution generated on the device (generating 1.4 GB with numpy would dominate the run)."""
+    g = torch.Generator(device=dev).manual_seed(seed)
+    yy = torch.linspace(0, 6, NFINE, device=dev)[:, None]
+    xx = torch.linspace(0, 6, NFINE, device=dev)[None, :]
+    ps = 8.6e4 + 1.4e4 * torch.sin(yy * 1.3) * torch.cos(xx * 1.1) + 1500 * torch.randn((NTILE, NFINE, NFINE), device=dev, generator=g)
+    ps = ps.clamp(5.0e4, 1.04e5)
+    b = torch.diff(torch.linspace(0, 1, KM + 1, device=dev) ** 1.6)
+    noise = 1 + 0.04 * (torch.rand((NTILE, KM, NFINE, NFINE), device=dev, generator=g) - 0.5)
+    delp = ((ps[:, None] - TOA) * b[None, :, None, None] * noise).float().contiguous()
+    area = (3.6e8 + 4.7e8 * torch.rand((NTILE, NFINE, NFINE), device=dev, generator=g)).float()
+    fields = [(180 + 140 * torch.rand((NTILE, KM, NFINE, NFINE), device=dev, generator=g)).float()]
+    fields += [(10 * torch.randn((NTILE, KM, NFINE, NFINE), device=dev, generator=g)).float() for _ in range(NFIELDS - 1)]
+    return delp, area, fields
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], None, set()
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 9:
+                continue
+            try:
+                sm.append(float(p[1]))
+                smax = float(p[2])
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_reference_step(sample, nthreads):
+    """One pass of the reference algorithm (CPU oracle: numpy restatement of regridz.py /
+    coarsen.py + the C restatement of mappm.f90) over the bounded sample."""
+    from oracle import vcm_ref as R
+
+    delp, area, fields = sample
+    d = {f"f{i}": x for i, x in enumerate(fields)}
+    reg, masked = R.regrid_to_area_weighted_pressure(d, delp, area[:, None], TOA, FACTOR, False, nthreads=nthreads)
+    outs = [R.weighted_block_average(reg[k], masked, FACTOR) for k in d]
+    outs.append(R.weighted_block_average(delp, area[:, None], FACTOR))
+    return outs
+
+
+def cpu_sample(seed):
+    # one of the six tiles, all 79 levels, all 4 fields: 1/6 of the C384 workload
+    delp, area, fields = synth_numpy(seed, ntile=1, km=KM, ny=NFINE, nx=NFINE)
+    pts = 1 * KM * NFINE * NFINE * NFIELDS
+    return (delp, area, fields), pts, "1 tile x 79 levels x 384 x 384 columns x 4 fields (1/6 of the C384 workload)"
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import vcm_ref as R
+
+    R.lib()
+    cores = os.cpu_count() or 1
+    sample, pts, desc = cpu_sample(0)
+    for _ in range(max(args.warmup, 1)):
+        cpu_reference_step(sample, cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_reference_step(sample, cores)
+    dt = (time.perf_counter() - t0) / args.steps
+    val = pts / dt
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C384->C48 pressure-level fv_core A-grid (delp + W,T,ua,va), f=8, kord=1, iv=1, "
+                               "extrapolate=False; each step = bounded sample: " + desc},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference stack (xarray/dask/xgcm + Fortran mappm) cannot run in this image; this is the CPU oracle "
+                "port: numpy block sums (single thread, as the reference forces dask single-threaded) + C mappm "
+                "with OpenMP over columns on all host cores",
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="exact", choices=["exact", "fast"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    from fv3net_b200 import core
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    mode = core.EXACT if args.mode == "exact" else core.FAST
+
+    delp, area, fields = synth_device(torch, 1000 + rank, dev)
+    cdim = NFINE // FACTOR
+    gathered = torch.empty((world, NFIELDS + 1, NTILE, KM, cdim, cdim), dtype=torch.float32, device=dev) if world > 1 else None
+
+    def step():
+        outs, dco = core.pressure_coarsen(fields, delp, area, FACTOR, TOA, mask_mode="phalf", mode=mode)
+        if world > 1:  # C1: collect only the small coarse outputs
+            mine = torch.stack(list(outs) + [dco])
+            dist.all_gather_into_tensor(gathered, mine)
+        return outs, dco
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = ev0.elapsed_time(ev1)
+    # kernel-only time (same launches, no collective) for the roofline of the fused kernel
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k0.record()
+    for _ in range(args.steps):
+        core.pressure_coarsen(fields, delp, area, FACTOR, TOA, mask_mode="phalf", mode=mode)
+    k1.record()
+    torch.cuda.synchronize()
+    kernel_ms = k0.elapsed_time(k1) / args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_per_step = ms / args.steps
+    value = world * points_per_step() / (ms_per_step * 1e-3)
+
+    # ---- end to end through the public API from pinned host buffers -------------------------
+    e2e = None
+    if not args.no_e2e:
+        h_delp = delp.cpu().pin_memory()
+        h_area = area.cpu().pin_memory()
+        h_fields = [x.cpu().pin_memory() for x in fields]
+        h_out = torch.empty((NFIELDS + 1, NTILE, KM, cdim, cdim), dtype=torch.float32).pin_memory()
+        h2d = h_delp.numel() * 4 + h_area.numel() * 4 + sum(x.numel() * 4 for x in h_fields)
+        d2h = h_out.numel() * 4
+
+        def e2e_step():
+            outs, dco = core.pressure_coarsen(h_fields, h_delp, h_area, FACTOR, TOA, mask_mode="phalf", mode=mode)
+            h_out.copy_(torch.stack(list(outs) + [dco]), non_blocking=True)
+            torch.cuda.synchronize()
+
+        n_e2e = max(3, min(args.steps, 5))
+        e2e_step()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            e2e_step()
+        e_ms = (time.perf_counter() - t0) * 1e3 / n_e2e
+        if world > 1:
+            t = torch.tensor([e_ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e_ms = float(t.item())
+        e2e = {"value": world * points_per_step() / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "ms_per_step": e_ms, "steps": n_e2e}
+        del h_delp, h_area, h_fields, h_out
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = measured_peak()
+    abytes = algorithmic_bytes()
+    achieved = abytes / (kernel_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get(f"pressure_coarsen_{args.mode}")
+        except Exception:
+            traffic = None
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C384->C48 pressure-level fv_core A-grid (delp + W,T,ua,va): 6 tiles x 79 levels x "
+                               "384 x 384 fp32, f=8, kord=1, iv=1, extrapolate=False, fused kernel",
+                   "arithmetic_mode": args.mode, "l2": "inputs (1.42 GB) larger than L2, no flush needed",
+                   "per_rank": "one synthetic timestep per GPU (weak)", "collective": "NCCL all_gather of coarse outputs" if world > 1 else "none"},
+        "clocks": clocks,
+        "e2e": e2e,
+        "gpu_launches": args.steps,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": traffic, "peak_source": peak_src, "kernel": "pressure_coarsen_kernel<NF=4,f32,f32,FX=8>",
+                     "algorithmic_bytes_per_launch": abytes, "kernel_ms": kernel_ms},
+    }
+    if not args.no_cpu_baseline and world == 1:
+        from oracle import vcm_ref as R
+
+        R.lib()
+        cores = os.cpu_count() or 1
+        sample, pts, desc = cpu_sample(0)
+        cpu_reference_step(sample, cores)
+        t0 = time.perf_counter()
+        reps = 3
+        for _ in range(reps):
+            cpu_reference_step(sample, cores)
+        dt = (time.perf_counter() - t0) / reps
+        line["cpu_baseline"] = {"value": pts / dt, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

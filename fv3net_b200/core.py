@@ -1,0 +1,401 @@
+"""Array-level host API of fv3net_b200: the arithmetic of vcm.cubedsphere's coarse-graining
+operators on device buffers.  Horizontal axes are the LAST two axes ``[..., y, x]`` (x contiguous,
+the layout of FV3 restart files); a vertical axis, where one exists, is axis -3.
+
+Inputs may be ``torch`` CUDA tensors (returned as CUDA tensors, nothing leaves the device) or
+numpy arrays (uploaded, result downloaded: numpy in -> numpy out, the reference's contract).
+Every function launches hand-written sm_100a kernels through the C ABI of ``libb200cs.so``
+(include/b200cs.h); there is no CPU path.
+
+Reference citations are relative to /root/reference/external/vcm/vcm/.
+"""
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import EXACT, FAST, MASK_NONE, MASK_PFULL, MASK_PHALF  # noqa: F401
+
+_DT = {torch.float32: _lib.F32, torch.float64: _lib.F64}
+_MASK = {None: MASK_NONE, "none": MASK_NONE, "phalf": MASK_PHALF, "pfull": MASK_PFULL}
+_OPS = {"sum": _lib.OP_SUM, "mean": _lib.OP_MEAN, "min": _lib.OP_MIN, "max": _lib.OP_MAX,
+        "median": _lib.OP_MEDIAN, "mode": _lib.OP_MODE}
+
+
+def device():
+    if not torch.cuda.is_available():
+        raise _lib.B200csError("fv3net_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _to_dev(a, floating=True):
+    """-> (tensor on device, was_numpy).  Integer / bool inputs become float64 like numpy's
+    true-division promotion in the reference expressions."""
+    was_np = not isinstance(a, torch.Tensor)
+    t = torch.as_tensor(np.ascontiguousarray(a)) if was_np else a
+    if floating and t.dtype not in _DT:
+        t = t.to(torch.float64)
+    if t.device.type != "cuda":
+        t = t.to(device(), non_blocking=True)
+    return t, was_np
+
+
+def _ret(t, was_np):
+    return t.cpu().numpy() if was_np else t
+
+
+def _promote(*ts):
+    return torch.float64 if any(t is not None and t.dtype == torch.float64 for t in ts) else torch.float32
+
+
+def _collapse(shape, strides, lo, hi):
+    """Stride of dims[lo:hi] merged into one axis, or None if they do not merge."""
+    dims = [(n, s) for n, s in zip(shape[lo:hi], strides[lo:hi]) if n != 1]
+    if not dims:
+        return 0
+    for (n0, s0), (n1, s1) in zip(dims[:-1], dims[1:]):
+        if s0 != s1 * n1:
+            return None
+    return dims[-1][1]
+
+
+def _canon4(ts, lead_shape):
+    """Views tensors (all expanded to lead_shape + (ny, nx)) as [B0, B1, ny, nx] with common
+    (B0, B1) and per-tensor element strides (s0, s1, sy).  Falls back to contiguous copies."""
+    nl = len(lead_shape)
+    for attempt in range(2):
+        for split in range(nl, -1, -1):
+            ok, strides = True, []
+            for t in ts:
+                if t.stride(-1) != 1 and t.shape[-1] != 1:
+                    ok = False
+                    break
+                s0 = _collapse(t.shape, t.stride(), 0, split)
+                s1 = _collapse(t.shape, t.stride(), split, nl)
+                if s0 is None or s1 is None:
+                    ok = False
+                    break
+                strides.append((s0, s1, t.stride(-2)))
+            if ok:
+                b0 = int(np.prod(lead_shape[:split], dtype=np.int64))
+                b1 = int(np.prod(lead_shape[split:], dtype=np.int64))
+                return ts, b0, b1, strides
+        ts = [t.contiguous() for t in ts]
+    raise AssertionError("unreachable")
+
+
+def _window(f, edge):
+    if edge is None:
+        return f, f, f, f
+    if edge == "x":
+        return 1, f, f, f  # fy, fx, ystep, xstep
+    if edge == "y":
+        return f, 1, f, f
+    raise ValueError(f"'edge' most be either 'x' or 'y'; got {edge}.")
+
+
+def weighted_block_average(obj, weights, coarsening_factor, weights2=None, edge=None):
+    """nansum(obj*W)/nansum(W) over windows of the last two axes (cubedsphere/coarsen.py:183-273).
+
+    W = weights, or weights2*weights when ``weights2`` is given (mass = delp*area formed on the
+    fly, cubedsphere/coarsen_restarts.py:400).  ``edge`` None: f x f blocks; 'x' / 'y': the
+    edge-weighted average (1-D windows along that axis, every f-th line across it).
+    weights (and weights2) broadcast against obj in the leading axes (numpy rules)."""
+    f = int(coarsening_factor)
+    fy, fx, ystep, xstep = _window(f, edge)
+    o, was_np = _to_dev(obj)
+    w, _ = _to_dev(weights)
+    v = _to_dev(weights2)[0] if weights2 is not None else None
+    ny, nx = o.shape[-2:]
+    tensors = [o, w] + ([v] if v is not None else [])
+    lead = torch.broadcast_shapes(*[t.shape[:-2] for t in tensors])
+    for t in tensors:
+        if tuple(t.shape[-2:]) != (ny, nx):
+            raise ValueError("obj and weights must share their horizontal extents")
+    tensors = [t.expand(lead + (ny, nx)) for t in tensors]
+    tensors, b0, b1, st = _canon4(tensors, lead)
+    if edge is None and (ny % f or nx % f):
+        raise ValueError(f"window {f} does not divide the horizontal extents {(ny, nx)}")
+    cy, cx = (ny - fy) // ystep + 1, (nx - fx) // xstep + 1
+    odt = _promote(*tensors)
+    out = torch.empty(lead + (cy, cx), dtype=odt, device=o.device)
+    lib = _lib.load()
+    o, w = tensors[0], tensors[1]
+    v = tensors[2] if v is not None else None
+    rc = lib.b200cs_weighted_block_average(
+        o.data_ptr(), _DT[o.dtype], _lib.i64arr(st[0]), w.data_ptr(), _DT[w.dtype], _lib.i64arr(st[1]),
+        v.data_ptr() if v is not None else None, _DT[v.dtype] if v is not None else 0,
+        _lib.i64arr(st[2]) if v is not None else None, out.data_ptr(), _DT[odt], b0, b1, ny, nx, fy, fx,
+        ystep, xstep, _stream())
+    _lib.check(rc, "weighted_block_average")
+    return _ret(out, was_np)
+
+
+def edge_weighted_block_average(obj, spacing, coarsening_factor, edge="x"):
+    """cubedsphere/coarsen.py:221-273 on ``[..., y, x]`` arrays."""
+    if edge not in ("x", "y"):
+        raise ValueError(f"'edge' most be either 'x' or 'y'; got {edge}.")
+    return weighted_block_average(obj, spacing, coarsening_factor, edge=edge)
+
+
+def block_reduce(obj, coarsening_factor, method="sum", skipna=True, edge=None, pad=False, cval=np.nan):
+    """Block reduction of the last two axes by ``method`` in sum/mean/min/max/median/mode.
+    Replaces horizontal_block_reduce / block_coarsen / block_edge_coarsen
+    (cubedsphere/coarsen.py:520-683,795-840; _skimage.py:125-202).  ``pad`` pads trailing edges
+    with ``cval`` (skimage semantics); dtype is preserved."""
+    if method not in _OPS:
+        raise ValueError(f"unsupported reduction {method!r}; supported: {sorted(_OPS)}")
+    f = int(coarsening_factor)
+    fy, fx, ystep, xstep = _window(f, edge)
+    o, was_np = _to_dev(obj)
+    o = o.contiguous()
+    ny, nx = o.shape[-2:]
+    lead = tuple(o.shape[:-2])
+    nb = int(np.prod(lead, dtype=np.int64))
+    if pad:
+        cy, cx = -(-ny // fy), -(-nx // fx)
+    else:
+        cy, cx = (ny - fy) // ystep + 1, (nx - fx) // xstep + 1
+    out = torch.empty(lead + (cy, cx), dtype=o.dtype, device=o.device)
+    rc = _lib.load().b200cs_block_reduce(o.data_ptr(), _DT[o.dtype], _lib.i64arr((ny * nx, nx)), out.data_ptr(),
+                                         nb, ny, nx, fy, fx, ystep, xstep, _OPS[method], int(bool(skipna)),
+                                         int(bool(pad)), float(cval), _stream())
+    _lib.check(rc, "block_reduce")
+    return _ret(out, was_np)
+
+
+def block_upsample(obj, upsampling_factor, axes=(-2, -1)):
+    """Repeat each element f times along the given horizontal axes; an odd-size axis is an
+    interface axis whose last element is not repeated (cubedsphere/coarsen.py:843-897)."""
+    f = int(upsampling_factor)
+    o, was_np = _to_dev(obj, floating=False)
+    nd = o.dim()
+    axes = tuple(a % nd for a in axes)
+    if not set(axes) <= {nd - 2, nd - 1}:
+        raise ValueError("block_upsample works on the last two axes")
+    if o.element_size() not in (4, 8):
+        o = o.to(torch.float64)
+    o = o.contiguous()
+    cy, cx = o.shape[-2:]
+    fy = f if (nd - 2) in axes else 1
+    fx = f if (nd - 1) in axes else 1
+    ys, xs = int(fy > 1 and cy % 2 == 1), int(fx > 1 and cx % 2 == 1)
+    ny = (cy - 1) * fy + 1 if ys else cy * fy
+    nx = (cx - 1) * fx + 1 if xs else cx * fx
+    out = torch.empty(tuple(o.shape[:-2]) + (ny, nx), dtype=o.dtype, device=o.device)
+    nb = int(np.prod(o.shape[:-2], dtype=np.int64))
+    rc = _lib.load().b200cs_block_upsample(o.data_ptr(), out.data_ptr(), o.element_size(), nb, cy, cx, fy, fx,
+                                           ys, xs, _stream())
+    _lib.check(rc, "block_upsample")
+    return _ret(out, was_np)
+
+
+def block_upsample_like(obj, reference_shape_yx):
+    """cubedsphere/coarsen.py:900-938: the factor is inferred from the x axis."""
+    nx_c, nx_f = obj.shape[-1], reference_shape_yx[1]
+    f = (nx_f - 1) // (nx_c - 1) if nx_c % 2 == 1 else nx_f // nx_c
+    return block_upsample(obj, f)
+
+
+def stagger(delp, axis, line_step=1):
+    """Centre -> edge interpolation across the six cube faces (xgcm ``grid.interp`` with
+    FV3_FACE_CONNECTIONS, cubedsphere/xgcm.py:7-34, regridz.py:118-132).  delp ``[6, ..., n, n]``;
+    axis 'y' -> ``[6, ..., n+1, n]``, 'x' -> ``[6, ..., n, n+1]``.  With line_step > 1 only lines
+    0, step, .. are produced, line-major: ``[6, ..., n/step+1, n]`` for both axes."""
+    d, was_np = _to_dev(delp)
+    if d.shape[0] != 6 or d.shape[-1] != d.shape[-2]:
+        raise ValueError("stagger needs a [6, ..., n, n] array (tile axis first)")
+    d = d.contiguous()
+    n = d.shape[-1]
+    nb1 = int(np.prod(d.shape[1:-2], dtype=np.int64))
+    ax = {"y": 0, "x": 1}[axis]
+    nl = n // line_step + 1
+    if ax == 0 or line_step > 1:
+        oshape = tuple(d.shape[:-2]) + (nl, n)
+    else:
+        oshape = tuple(d.shape[:-2]) + (n, nl)
+    out = torch.empty(oshape, dtype=d.dtype, device=d.device)
+    rc = _lib.load().b200cs_stagger(d.data_ptr(), out.data_ptr(), _DT[d.dtype], nb1, n, ax, int(line_step), _stream())
+    _lib.check(rc, "stagger")
+    return _ret(out, was_np)
+
+
+def pressure_at_interface(delp, toa_pressure=300.0, z_axis=-3):
+    """calc/thermo/vertically_dependent.py:41-66: [toa, toa+cumsum(delp)] along z (NaN as 0)."""
+    d, was_np = _to_dev(delp)
+    nd = d.dim()
+    z = z_axis % nd
+    dz = d.movedim(z, -3) if nd >= 3 else d.unsqueeze(-1).unsqueeze(-1).movedim(z, -3)
+    dz = dz.contiguous()
+    km = dz.shape[-3]
+    ncol = dz.shape[-2] * dz.shape[-1]
+    nb0 = int(np.prod(dz.shape[:-3], dtype=np.int64))
+    out = torch.empty(tuple(dz.shape[:-3]) + (km + 1,) + tuple(dz.shape[-2:]), dtype=d.dtype, device=d.device)
+    rc = _lib.load().b200cs_pressure_at_interface(dz.data_ptr(), _DT[d.dtype], _lib.i64arr((km * ncol, ncol)),
+                                                  out.data_ptr(), nb0, km, ncol, float(toa_pressure), _stream())
+    _lib.check(rc, "pressure_at_interface")
+    out = out.movedim(-3, z) if nd >= 3 else out.movedim(-3, z).squeeze(-1).squeeze(-1)
+    return _ret(out, was_np)
+
+
+def mappm(pe1, q1, pe2, i1=1, i2=None, iv=1, kord=1, ptop=0.0):
+    """Drop-in for the f2py call ``mappm.mappm(pe1[ncol,km+1], q1[ncol,km], pe2[ncol,kn+1], i1,
+    i2, iv, kord, ptop)`` -> float32 ``[ncol, kn]`` (external/mappm/mappm/mappm.f90:10;
+    cubedsphere/regridz.py:329-334).  Scalars are coerced with int() like f2py does
+    (tests/test_mappm.py:9-13 passes floats); ptop is unused, as in the Fortran."""
+    p1, was_np = _to_dev(pe1)
+    q, _ = _to_dev(q1)
+    p2, _ = _to_dev(pe2)
+    p1, q, p2 = (t.to(torch.float32).contiguous() for t in (p1, q, p2))
+    ncol, km = q.shape
+    if p1.shape != (ncol, km + 1) or p2.shape[0] != ncol:
+        raise ValueError("mappm: expected pe1[ncol,km+1], q1[ncol,km], pe2[ncol,kn+1]")
+    kn = p2.shape[1] - 1
+    out = torch.empty((ncol, kn), dtype=torch.float32, device=q.device)
+    _mappm_raw(p1, (km + 1, 1), q, (km, 1), p2, (kn + 1, 1), out, (kn, 1), ncol, km, kn, int(iv), int(kord))
+    return _ret(out, was_np)
+
+
+def _mappm_raw(p1, s1, q, sq, p2, s2, out, so, ncol, km, kn, iv, kord):
+    lib = _lib.load()
+    ws, nbytes = None, 0
+    if kord > 6:
+        nbytes = lib.b200cs_mappm_workspace_bytes(ncol, km)
+        ws = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=q.device)
+    rc = lib.b200cs_mappm(p1.data_ptr(), s1[0], s1[1], q.data_ptr(), sq[0], sq[1], p2.data_ptr(), s2[0], s2[1],
+                          out.data_ptr(), so[0], so[1], ncol, km, kn, iv, kord,
+                          ws.data_ptr() if ws is not None else None, nbytes, _stream())
+    _lib.check(rc, "mappm")
+
+
+def regrid_vertical(p_in, f_in, p_out, iv=1, kord=1, z_axis=-3):
+    """cubedsphere/regridz.py:223-338 on arrays with the vertical axis at ``z_axis`` and all other
+    axes equal.  The restart layout ``[..., z, y, x]`` is consumed in place through strides (no
+    transposes); output float32 like mappm's."""
+    pi, was_np = _to_dev(p_in)
+    fi, _ = _to_dev(f_in)
+    po, _ = _to_dev(p_out)
+    nd = fi.dim()
+    z = z_axis % nd
+    if pi.shape[z] - 1 != fi.shape[z]:
+        raise ValueError("f_in must have a vertical dimension one shorter than p_in")
+    rest = lambda t: tuple(s for i, s in enumerate(t.shape) if i != z)  # noqa: E731
+    if rest(pi) != rest(fi) or rest(po) != rest(fi):
+        raise ValueError("All dimensions except vertical must be same size for p_in, f_in and p_out")
+    # bring to [outer, z, inner] contiguous, fp32 (f2py casts)
+    outer = int(np.prod(fi.shape[:z], dtype=np.int64))
+    inner = int(np.prod(fi.shape[z + 1:], dtype=np.int64))
+    pi, fi, po = (t.to(torch.float32).contiguous() for t in (pi, fi, po))
+    km, kn = fi.shape[z], po.shape[z] - 1
+    oshape = list(fi.shape)
+    oshape[z] = kn
+    out = torch.empty(oshape, dtype=torch.float32, device=fi.device)
+    for b in range(outer):  # each outer slab is a [z, inner] matrix: col stride 1, level stride inner
+        off = lambda t, nz: t.view(outer, nz, inner)[b]  # noqa: E731
+        _mappm_raw(off(pi, km + 1), (1, inner), off(fi, km), (1, inner), off(po, kn + 1), (1, inner),
+                   off(out, kn), (1, inner), inner, km, kn, int(iv), int(kord))
+    return _ret(out, was_np)
+
+
+def mask_weights(weights, p_coarse_on_fine, phalf_fine, mask_mode="phalf"):
+    """cubedsphere/regridz.py:200-220 for ``[..., z, y, x]`` arrays; weights ``[..., y, x]``.
+    mask_mode 'phalf' compares phalf_coarse_on_fine[k+1], 'pfull' pfull_coarse_on_fine[k]."""
+    w, was_np = _to_dev(weights)
+    pc, _ = _to_dev(p_coarse_on_fine)
+    pf, _ = _to_dev(phalf_fine)
+    dt = _promote(pc, pf)
+    pc, pf, w = pc.to(dt).contiguous(), pf.to(dt).contiguous(), w.contiguous()
+    km = pf.shape[-3] - 1
+    ncol = pf.shape[-2] * pf.shape[-1]
+    lead = tuple(pf.shape[:-3])
+    nb0 = int(np.prod(lead, dtype=np.int64))
+    w = w.expand(lead + tuple(w.shape[-2:])).contiguous()
+    out = torch.empty(lead + (km,) + tuple(pf.shape[-2:]), dtype=w.dtype, device=w.device)
+    rc = _lib.load().b200cs_mask_weights(w.data_ptr(), _DT[w.dtype], pc.data_ptr(), pf.data_ptr(), _DT[dt],
+                                         out.data_ptr(), nb0, km, ncol, _MASK[mask_mode], _stream())
+    _lib.check(rc, "mask_weights")
+    return _ret(out, was_np)
+
+
+def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.0, mask_mode="phalf",
+                     edge_lines=False, iv=1, kord=1, mode=EXACT, return_delp_coarse=True):
+    """Fused pressure-level coarse-graining (one pass over the fine data).
+
+    Equivalent to regrid_to_area_weighted_pressure + weighted_block_average with the masked
+    weights (cubedsphere/regridz.py:31-220, cubedsphere/coarsen_restarts.py:485-534,934-959), or
+    with mask_mode='none' to Grid.pressure_level_average of fine_res_budget
+    (workflows/fine_res_budget/budget/budgets.py:49-57).
+
+    fields: list of ``[B, km, ny, nx]`` arrays (B = tiles); delp same shape; weights ``[B, ny, nx]``.
+    edge_lines: windows are 1 x f (the rows are the kept lines of a D-grid wind component).
+    Returns (list of coarse fields ``[B, km, cy, cx]``, coarse delp or None)."""
+    f = int(coarsening_factor)
+    was_np = not isinstance(delp, torch.Tensor)
+    d, _ = _to_dev(delp)
+    w, _ = _to_dev(weights)
+    fs = [_to_dev(x)[0] for x in fields]
+    if d.dim() != 4 or w.dim() != 3:
+        raise ValueError("pressure_coarsen: delp must be [B, km, ny, nx] and weights [B, ny, nx]")
+    nb0, km, ny, nx = d.shape
+    fdt = _promote(*fs) if fs else torch.float32
+    fs = [x.to(fdt) for x in fs]
+
+    def strided(t):
+        if t.stride(-1) != 1:
+            t = t.contiguous()
+        return t
+
+    d, w = strided(d), strided(w)
+    fs = [strided(x) for x in fs]
+    if fs:
+        s0 = tuple(fs[0].stride()[:3])
+        fs = [x if tuple(x.stride()[:3]) == s0 else x.contiguous() for x in fs]
+        if any(tuple(x.stride()[:3]) != tuple(fs[0].stride()[:3]) for x in fs):
+            fs = [x.contiguous() for x in fs]
+    for x in fs:
+        if tuple(x.shape) != (nb0, km, ny, nx):
+            raise ValueError("pressure_coarsen: every field must have delp's shape")
+    if tuple(w.shape) != (nb0, ny, nx):
+        raise ValueError("pressure_coarsen: weights must be [B, ny, nx]")
+    fy = 1 if edge_lines else f
+    cy, cx = ny // fy, nx // f
+    wdt = w.dtype
+    cdt = _promote(d, w)
+    outs = [torch.empty((nb0, km, cy, cx), dtype=wdt, device=d.device) for _ in fs]
+    dco = torch.empty((nb0, km, cy, cx), dtype=cdt, device=d.device) if return_delp_coarse else None
+    lib = _lib.load()
+    rc = lib.b200cs_pressure_coarsen(
+        len(fs), _lib.ptrarr([x.data_ptr() for x in fs]), _DT[fdt], _lib.i64arr(fs[0].stride()[:3] if fs else (0, 0, 0)),
+        d.data_ptr(), _DT[d.dtype], _lib.i64arr(d.stride()[:3]), w.data_ptr(), _DT[wdt], _lib.i64arr(w.stride()[:2]),
+        _lib.ptrarr([o.data_ptr() for o in outs]), dco.data_ptr() if dco is not None else None,
+        nb0, km, ny, nx, fy, f, float(toa_pressure), _MASK[mask_mode], int(iv), int(kord), int(mode), _stream())
+    _lib.check(rc, "pressure_coarsen")
+    if was_np:
+        return [o.cpu().numpy() for o in outs], (dco.cpu().numpy() if dco is not None else None)
+    return outs, dco
+
+
+def gather_columns(a, step):
+    """[..., ny, nx] -> [..., (nx-1)//step+1, ny]: every step-th x column as a contiguous line."""
+    t, was_np = _to_dev(a, floating=False)
+    t = t.contiguous()
+    lead = tuple(t.shape[:-2])
+    ny, nx = t.shape[-2:]
+    nl = (nx - 1) // step + 1
+    out = torch.empty(lead + (nl, ny), dtype=t.dtype, device=t.device)
+    nb = int(np.prod(lead, dtype=np.int64))
+    lib = _lib.load()
+    flat_in, flat_out = t.view(nb, ny, nx), out.view(nb, nl, ny)
+    for lo in range(0, nb, 65535):  # grid.z is limited to 65535 slabs per launch
+        n = min(65535, nb - lo)
+        rc = lib.b200cs_gather_columns(flat_in[lo:].data_ptr(), _lib.i64arr((ny * nx, nx)), flat_out[lo:].data_ptr(),
+                                       t.element_size(), n, ny, nx, int(step), _stream())
+        _lib.check(rc, "gather_columns")
+    return _ret(out, was_np)
+
+
+def transpose_last2(a):
+    return gather_columns(a, 1)

@@ -1,0 +1,470 @@
+// block_ops.cu -- horizontal block kernels of libb200cs (sm_100a):
+//   K1/K2  weighted block average / edge-weighted block average
+//   K3     generic block reduce (sum/mean/min/max/median/mode, NaN-skipping, padding)
+//   K4     block upsample
+//   plus the small layout helpers used by the D-grid pressure path.
+// All are HBM-bound streaming kernels: 128-bit coalesced loads, every fine byte read once,
+// numerator / denominator / divide fused in one pass.  Compiled with -fmad=false so that
+// x*w is rounded before it is summed, exactly like numpy's materialised `obj * weights`.
+#include "common.cuh"
+
+namespace b200cs {
+
+// ---------------------------------------------------------------------------------------
+// K1 generic: one thread per (output cell, level).  Any window, any dtype mix.
+// ---------------------------------------------------------------------------------------
+template <typename TO, typename TW, typename TW2, bool HAS_W2>
+__global__ void __launch_bounds__(256)
+wba_generic_kernel(const TO* __restrict__ obj, int64_t so0, int64_t so1, int64_t soy,
+                   const TW* __restrict__ w, int64_t sw0, int64_t sw1, int64_t swy,
+                   const TW2* __restrict__ w2, int64_t sv0, int64_t sv1, int64_t svy,
+                   typename Promote<TO, typename Promote<TW, TW2>::type>::type* __restrict__ out,
+                   int64_t nb0, int64_t nb1, int64_t cy, int64_t cx, int fy, int fx, int ystep,
+                   int xstep) {
+    using TD = typename Promote<TW, TW2>::type;  // weight dtype (mass = delp*area promotes)
+    using TN = typename Promote<TO, TD>::type;   // product / output dtype
+    const int64_t total = nb0 * nb1 * cy * cx;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = idx % cx;
+        const int64_t j = (idx / cx) % cy;
+        const int64_t b1 = (idx / (cx * cy)) % nb1;
+        const int64_t b0 = idx / (cx * cy * nb1);
+        TN acc = TN(0);
+        TD dacc = TD(0);
+        for (int r = 0; r < fy; r++) {
+            const int64_t y = j * ystep + r, x = i * xstep;
+            const TO* xo = obj + b0 * so0 + b1 * so1 + y * soy + x;
+            const TW* xw = w + b0 * sw0 + b1 * sw1 + y * swy + x;
+            const TW2* xv = HAS_W2 ? (w2 + b0 * sv0 + b1 * sv1 + y * svy + x) : nullptr;
+            auto wt = [&](int c) -> TD {
+                if (HAS_W2) return (TD)xv[c] * (TD)xw[c];
+                return (TD)xw[c];
+            };
+            acc += rowsum_numpy<TN>(fx, [&](int c) { return nan_to_zero((TN)xo[c] * (TN)wt(c)); });
+            dacc += rowsum_numpy<TD>(fx, [&](int c) { return nan_to_zero(wt(c)); });
+        }
+        out[idx] = acc / (TN)dacc;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// K1 fast path: 8x8 windows, fp32 everywhere, 16-byte aligned rows.  One thread owns one
+// coarse cell for LV consecutive levels, so a 2-D weight row (two float4) is loaded once and
+// reused LV times, and the weight sum is formed once.  Row sums use the 8-wide pairwise tree
+// ((p0+p1)+(p2+p3))+((p4+p5)+(p6+p7)), rows are added in order: numpy's order exactly.
+// W3D: weights carry a level stride (masked 3-D weights) -> per-level weight rows and sums.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ float tree8(const float4& a, const float4& b) {
+    return ((a.x + a.y) + (a.z + a.w)) + ((b.x + b.y) + (b.z + b.w));
+}
+__device__ __forceinline__ float4 mul_nz(const float4& x, const float4& w) {
+    return make_float4(nan_to_zero(x.x * w.x), nan_to_zero(x.y * w.y), nan_to_zero(x.z * w.z),
+                       nan_to_zero(x.w * w.w));
+}
+__device__ __forceinline__ float4 nz4(const float4& w) {
+    return make_float4(nan_to_zero(w.x), nan_to_zero(w.y), nan_to_zero(w.z), nan_to_zero(w.w));
+}
+__device__ __forceinline__ float4 ldg4(const float* p) {
+    return __ldg(reinterpret_cast<const float4*>(p));
+}
+
+template <int LV, bool W3D, bool HAS_W2>
+__global__ void __launch_bounds__(256)
+wba8_f32_kernel(const float* __restrict__ obj, int64_t so0, int64_t so1, int64_t soy,
+                const float* __restrict__ w, int64_t sw0, int64_t sw1, int64_t swy,
+                const float* __restrict__ w2, int64_t sv0, int64_t sv1, int64_t svy,
+                float* __restrict__ out, int64_t nb0, int64_t nb1, int64_t cy, int64_t cx) {
+    const int64_t ncell = nb0 * cy * cx;
+    const int64_t cell = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (cell >= ncell) return;
+    const int64_t i = cell % cx, j = (cell / cx) % cy, b0 = cell / (cx * cy);
+    const int64_t l0 = (int64_t)blockIdx.y * LV;
+    const float* xo = obj + b0 * so0 + l0 * so1 + (j * 8) * soy + i * 8;
+    const float* xw = w + b0 * sw0 + (W3D ? l0 * sw1 : 0) + (j * 8) * swy + i * 8;
+    const float* xv = HAS_W2 ? (w2 + b0 * sv0 + l0 * sv1 + (j * 8) * svy + i * 8) : nullptr;
+    float acc[LV], den[LV];
+#pragma unroll
+    for (int l = 0; l < LV; l++) { acc[l] = 0.f; den[l] = 0.f; }
+#pragma unroll 2
+    for (int r = 0; r < 8; r++) {
+        float4 wa, wb;
+        if (!W3D && !HAS_W2) {
+            wa = ldg4(xw + r * swy);
+            wb = ldg4(xw + r * swy + 4);
+            den[0] += tree8(nz4(wa), nz4(wb));
+        }
+#pragma unroll
+        for (int l = 0; l < LV; l++) {
+            if (l0 + l < nb1) {
+                if (W3D || HAS_W2) {
+                    wa = ldg4(xw + (W3D ? l * sw1 : 0) + r * swy);
+                    wb = ldg4(xw + (W3D ? l * sw1 : 0) + r * swy + 4);
+                    if (HAS_W2) {  // mass = delp * area, rounded before use
+                        float4 va = ldg4(xv + l * sv1 + r * svy), vb = ldg4(xv + l * sv1 + r * svy + 4);
+                        wa = make_float4(va.x * wa.x, va.y * wa.y, va.z * wa.z, va.w * wa.w);
+                        wb = make_float4(vb.x * wb.x, vb.y * wb.y, vb.z * wb.z, vb.w * wb.w);
+                    }
+                    den[l] += tree8(nz4(wa), nz4(wb));
+                }
+                float4 xa = ldg4(xo + l * so1 + r * soy), xb = ldg4(xo + l * so1 + r * soy + 4);
+                acc[l] += tree8(mul_nz(xa, wa), mul_nz(xb, wb));
+            }
+        }
+    }
+#pragma unroll
+    for (int l = 0; l < LV; l++)
+        if (l0 + l < nb1)
+            out[((b0 * nb1 + l0 + l) * cy + j) * cx + i] = acc[l] / ((W3D || HAS_W2) ? den[l] : den[0]);
+}
+
+template <typename TO, typename TW, typename TW2, bool HAS_W2>
+static int launch_wba_generic(const void* obj, const int64_t* so, const void* w, const int64_t* sw,
+                              const void* w2, const int64_t* sv, void* out, int64_t nb0, int64_t nb1,
+                              int64_t cy, int64_t cx, int fy, int fx, int ystep, int xstep,
+                              cudaStream_t st) {
+    using TD = typename Promote<TW, TW2>::type;
+    using TN = typename Promote<TO, TD>::type;
+    const int64_t total = nb0 * nb1 * cy * cx;
+    if (total == 0) return B200CS_OK;
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > 148LL * 64) blocks = 148LL * 64;
+    wba_generic_kernel<TO, TW, TW2, HAS_W2><<<(unsigned)blocks, 256, 0, st>>>(
+        (const TO*)obj, so[0], so[1], so[2], (const TW*)w, sw[0], sw[1], sw[2], (const TW2*)w2,
+        HAS_W2 ? sv[0] : 0, HAS_W2 ? sv[1] : 0, HAS_W2 ? sv[2] : 0, (TN*)out, nb0, nb1, cy, cx, fy, fx,
+        ystep, xstep);
+    return check_launch("weighted_block_average");
+}
+
+template <typename TO, typename TW>
+static int dispatch_w2(const void* obj, const int64_t* so, const void* w, const int64_t* sw,
+                       const void* w2, int w2_dtype, const int64_t* sv, void* out, int64_t nb0,
+                       int64_t nb1, int64_t cy, int64_t cx, int fy, int fx, int ystep, int xstep,
+                       cudaStream_t st) {
+    if (!w2)
+        return launch_wba_generic<TO, TW, TW, false>(obj, so, w, sw, nullptr, sv, out, nb0, nb1, cy, cx,
+                                                     fy, fx, ystep, xstep, st);
+    if (w2_dtype == B200CS_F32)
+        return launch_wba_generic<TO, TW, float, true>(obj, so, w, sw, w2, sv, out, nb0, nb1, cy, cx, fy,
+                                                       fx, ystep, xstep, st);
+    return launch_wba_generic<TO, TW, double, true>(obj, so, w, sw, w2, sv, out, nb0, nb1, cy, cx, fy,
+                                                    fx, ystep, xstep, st);
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+// ---------------------------------------------------------------------------------------
+// K3 generic block reduce: thread per output cell; window gathered into local memory for
+// median / mode (window <= 256 elements), streamed otherwise.
+// ---------------------------------------------------------------------------------------
+constexpr int kMaxSortWindow = 256;
+
+template <typename T>
+__global__ void __launch_bounds__(128)
+block_reduce_kernel(const T* __restrict__ obj, int64_t s0, int64_t sy, T* __restrict__ out, int64_t nb,
+                    int64_t ny, int64_t nx, int64_t cy, int64_t cx, int fy, int fx, int ystep,
+                    int xstep, int op, int skipna, T cval) {
+    const int64_t total = nb * cy * cx;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = idx % cx, j = (idx / cx) % cy, b = idx / (cx * cy);
+        const T* base = obj + b * s0;
+        auto at = [&](int r, int c) -> T {
+            const int64_t y = j * ystep + r, x = i * (int64_t)xstep + c;
+            return (y < ny && x < nx) ? base[y * sy + x] : cval;  // trailing-edge padding
+        };
+        T res;
+        if (op == B200CS_OP_SUM || op == B200CS_OP_MEAN) {
+            // numpy order: pairwise along the window row, rows added sequentially
+            T acc = T(0);
+            int64_t cnt = 0;
+            for (int r = 0; r < fy; r++) {
+                acc += rowsum_numpy<T>(fx, [&](int c) {
+                    T v = at(r, c);
+                    if (skipna) { if (v == v) cnt++; return nan_to_zero(v); }
+                    return v;
+                });
+            }
+            if (op == B200CS_OP_SUM) res = acc;
+            else res = skipna ? acc / (T)cnt : acc / (T)((int64_t)fy * fx);
+        } else if (op == B200CS_OP_MIN || op == B200CS_OP_MAX) {
+            bool any = false, sawnan = false;
+            T m = T(0);
+            for (int r = 0; r < fy; r++)
+                for (int c = 0; c < fx; c++) {
+                    T v = at(r, c);
+                    if (v != v) { sawnan = true; continue; }
+                    if (!any) { m = v; any = true; }
+                    else if (op == B200CS_OP_MIN ? (v < m) : (v > m)) m = v;
+                }
+            res = ((sawnan && !skipna) || !any) ? (T)NAN : m;
+        } else {
+            // median / mode: insertion sort of the (non-NaN) window in local memory
+            T buf[kMaxSortWindow];
+            int n = 0;
+            bool sawnan = false;
+            for (int r = 0; r < fy; r++)
+                for (int c = 0; c < fx; c++) {
+                    T v = at(r, c);
+                    if (v != v) { sawnan = true; continue; }
+                    int p = n++;
+                    while (p > 0 && buf[p - 1] > v) { buf[p] = buf[p - 1]; p--; }
+                    buf[p] = v;
+                }
+            if ((sawnan && !skipna) || n == 0) {
+                res = (T)NAN;
+            } else if (op == B200CS_OP_MEDIAN) {
+                // np.median: mean of the two middle elements for even n
+                res = (n & 1) ? buf[n / 2] : (buf[n / 2 - 1] + buf[n / 2]) / T(2);
+            } else {  // mode: most frequent, ties -> smallest (scipy.stats.mode)
+                T best = buf[0];
+                int bestc = 0, run = 0;
+                for (int p = 0; p < n; p++) {
+                    run = (p > 0 && buf[p] == buf[p - 1]) ? run + 1 : 1;
+                    if (run > bestc) { bestc = run; best = buf[p]; }
+                }
+                res = best;
+            }
+        }
+        out[idx] = res;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// K4 block upsample (repeat); 4- or 8-byte elements.
+// ---------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+upsample_kernel(const T* __restrict__ in, T* __restrict__ out, int64_t nb, int64_t cy, int64_t cx,
+                int64_t ny, int64_t nx, int fy, int fx) {
+    const int64_t total = nb * ny * nx;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t x = idx % nx, y = (idx / nx) % ny, b = idx / (nx * ny);
+        // a staggered axis has (c-1)*f+1 points: index/f maps the last point onto c-1
+        out[idx] = in[(b * cy + y / fy) * cx + x / fx];
+    }
+}
+
+// gathers columns 0, step, 2*step.. of [nb, ny, nx] into line-major [nb, nlines, ny]
+template <typename T>
+__global__ void __launch_bounds__(256)
+gather_columns_kernel(const T* __restrict__ in, int64_t s0, int64_t sy, T* __restrict__ out, int64_t nb,
+                      int64_t ny, int64_t nlines, int step) {
+    // tile: 32 lines x 32 rows through shared memory so both sides stay coalesced-ish
+    __shared__ T tile[32][33];
+    const int64_t b = blockIdx.z;
+    const int64_t y0 = (int64_t)blockIdx.y * 32, l0 = (int64_t)blockIdx.x * 32;
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        const int64_t y = y0 + r, l = l0 + threadIdx.x;
+        if (y < ny && l < nlines) tile[r][threadIdx.x] = in[b * s0 + y * sy + l * step];
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        const int64_t l = l0 + r, y = y0 + threadIdx.x;
+        if (y < ny && l < nlines) out[(b * nlines + l) * ny + y] = tile[threadIdx.x][r];
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+pressure_interface_kernel(const T* __restrict__ delp, int64_t s0, int64_t sl, T* __restrict__ out,
+                          int64_t nb0, int64_t km, int64_t ncol, T toa) {
+    const int64_t total = nb0 * ncol;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t c = idx % ncol, b = idx / ncol;
+        T acc = toa;
+        T* o = out + b * (km + 1) * ncol + c;
+        o[0] = acc;
+        for (int64_t k = 0; k < km; k++) {
+            acc += nan_to_zero(delp[b * s0 + k * sl + c]);  // xarray cumsum == nancumsum
+            o[(k + 1) * ncol] = acc;
+        }
+    }
+}
+
+template <typename TW, typename TP>
+__global__ void __launch_bounds__(256)
+mask_weights_kernel(const TW* __restrict__ w, const TP* __restrict__ pc, const TP* __restrict__ pf,
+                    TW* __restrict__ out, int64_t nb0, int64_t km, int64_t ncol, int mode) {
+    const int64_t total = nb0 * km * ncol;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t c = idx % ncol, k = (idx / ncol) % km, b = idx / (ncol * km);
+        const TP surf = pf[(b * (km + 1) + km) * ncol + c];
+        const TP p = (mode == B200CS_MASK_PHALF) ? pc[(b * (km + 1) + k + 1) * ncol + c]
+                                                 : pc[(b * km + k) * ncol + c];
+        out[idx] = (mode == B200CS_MASK_NONE || p < surf) ? w[b * ncol + c] : TW(0);
+    }
+}
+
+static unsigned grid_for(int64_t total, int threads) {
+    int64_t blocks = (total + threads - 1) / threads;
+    const int64_t cap = 148LL * 32;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (unsigned)blocks;
+}
+
+}  // namespace b200cs
+
+using namespace b200cs;
+
+extern "C" int b200cs_weighted_block_average(const void* obj, int obj_dtype, const int64_t so[3],
+                                             const void* w, int w_dtype, const int64_t sw[3],
+                                             const void* w2, int w2_dtype, const int64_t sv[3],
+                                             void* out, int out_dtype, int64_t nb0, int64_t nb1,
+                                             int64_t ny, int64_t nx, int fy, int fx, int ystep,
+                                             int xstep, void* stream) {
+    B200CS_REQUIRE(obj && w && out && so && sw, "weighted_block_average: NULL argument");
+    B200CS_REQUIRE(!w2 || sv, "weighted_block_average: w2 given without strides");
+    B200CS_REQUIRE(fy >= 1 && fx >= 1 && ystep >= 1 && xstep >= 1, "weighted_block_average: bad window");
+    B200CS_REQUIRE(fx <= 128, "weighted_block_average: fx > 128 not supported (numpy pairwise recursion)");
+    B200CS_REQUIRE(nb0 >= 0 && nb1 >= 0 && ny >= fy && nx >= fx, "weighted_block_average: bad extents");
+    B200CS_REQUIRE((obj_dtype | 1) == 1 && (w_dtype | 1) == 1 && (!w2 || (w2_dtype | 1) == 1),
+                   "weighted_block_average: dtype must be F32 or F64");
+    const int want = (obj_dtype == B200CS_F64 || w_dtype == B200CS_F64 || (w2 && w2_dtype == B200CS_F64))
+                         ? B200CS_F64 : B200CS_F32;
+    B200CS_REQUIRE(out_dtype == want, "weighted_block_average: out_dtype must be the numpy promotion (%d)", want);
+    const int64_t cy = (ny - fy) / ystep + 1, cx = (nx - fx) / xstep + 1;
+    cudaStream_t st = as_stream(stream);
+
+    // fast path: 8x8 fp32 blocks with 16-byte aligned rows
+    const bool all32 = obj_dtype == B200CS_F32 && w_dtype == B200CS_F32 && (!w2 || w2_dtype == B200CS_F32);
+    const bool geo8 = fy == 8 && fx == 8 && ystep == 8 && xstep == 8 && ny % 8 == 0 && nx % 8 == 0;
+    auto s4 = [](const int64_t* s) { return s[0] % 4 == 0 && s[1] % 4 == 0 && s[2] % 4 == 0; };
+    if (all32 && geo8 && aligned16(obj) && aligned16(w) && s4(so) && s4(sw) &&
+        (!w2 || (aligned16(w2) && s4(sv))) && nb0 * nb1 * cy * cx > 0) {
+        const int64_t ncell = nb0 * cy * cx;
+        const bool w3d = sw[1] != 0;
+        constexpr int LV = 4;
+        dim3 grid((unsigned)((ncell + 127) / 128), 1, 1);
+#define B200CS_WBA8(LVV, W3, H2)                                                                     \
+    grid.y = (unsigned)((nb1 + LVV - 1) / LVV);                                                      \
+    wba8_f32_kernel<LVV, W3, H2><<<grid, 128, 0, st>>>((const float*)obj, so[0], so[1], so[2],       \
+                                                       (const float*)w, sw[0], sw[1], sw[2],         \
+                                                       (const float*)w2, w2 ? sv[0] : 0,             \
+                                                       w2 ? sv[1] : 0, w2 ? sv[2] : 0, (float*)out,  \
+                                                       nb0, nb1, cy, cx)
+        if (w2) { if (w3d) { B200CS_WBA8(2, true, true); } else { B200CS_WBA8(2, false, true); } }
+        else if (w3d) { B200CS_WBA8(2, true, false); }
+        else { B200CS_WBA8(LV, false, false); }
+#undef B200CS_WBA8
+        return check_launch("weighted_block_average(8x8 f32)");
+    }
+
+    if (obj_dtype == B200CS_F32 && w_dtype == B200CS_F32)
+        return dispatch_w2<float, float>(obj, so, w, sw, w2, w2_dtype, sv, out, nb0, nb1, cy, cx, fy, fx, ystep, xstep, st);
+    if (obj_dtype == B200CS_F32 && w_dtype == B200CS_F64)
+        return dispatch_w2<float, double>(obj, so, w, sw, w2, w2_dtype, sv, out, nb0, nb1, cy, cx, fy, fx, ystep, xstep, st);
+    if (obj_dtype == B200CS_F64 && w_dtype == B200CS_F32)
+        return dispatch_w2<double, float>(obj, so, w, sw, w2, w2_dtype, sv, out, nb0, nb1, cy, cx, fy, fx, ystep, xstep, st);
+    return dispatch_w2<double, double>(obj, so, w, sw, w2, w2_dtype, sv, out, nb0, nb1, cy, cx, fy, fx, ystep, xstep, st);
+}
+
+extern "C" int b200cs_block_reduce(const void* obj, int dtype, const int64_t s[2], void* out, int64_t nb,
+                                   int64_t ny, int64_t nx, int fy, int fx, int ystep, int xstep, int op,
+                                   int skipna, int pad, double cval, void* stream) {
+    B200CS_REQUIRE(obj && out && s, "block_reduce: NULL argument");
+    B200CS_REQUIRE(fy >= 1 && fx >= 1 && ystep >= 1 && xstep >= 1, "block_reduce: bad window");
+    B200CS_REQUIRE(fx <= 128, "block_reduce: fx > 128 not supported");
+    B200CS_REQUIRE(op >= B200CS_OP_SUM && op <= B200CS_OP_MODE, "block_reduce: unknown op %d", op);
+    B200CS_REQUIRE(dtype == B200CS_F32 || dtype == B200CS_F64, "block_reduce: dtype must be F32 or F64");
+    if ((op == B200CS_OP_MEDIAN || op == B200CS_OP_MODE) && (int64_t)fy * fx > kMaxSortWindow)
+        return set_err(B200CS_EUNSUPPORTED, "block_reduce: median/mode window %d x %d exceeds %d elements",
+                       fy, fx, kMaxSortWindow);
+    int64_t cy, cx;
+    if (pad) {
+        B200CS_REQUIRE(ystep == fy && xstep == fx, "block_reduce: padding needs non-overlapping windows");
+        cy = (ny + fy - 1) / fy; cx = (nx + fx - 1) / fx;
+    } else {
+        B200CS_REQUIRE(ny >= fy && nx >= fx, "block_reduce: window larger than array");
+        cy = (ny - fy) / ystep + 1; cx = (nx - fx) / xstep + 1;
+    }
+    const int64_t total = nb * cy * cx;
+    if (total == 0) return B200CS_OK;
+    cudaStream_t st = as_stream(stream);
+    if (dtype == B200CS_F32)
+        block_reduce_kernel<float><<<grid_for(total, 128), 128, 0, st>>>((const float*)obj, s[0], s[1], (float*)out,
+            nb, ny, nx, cy, cx, fy, fx, ystep, xstep, op, skipna, (float)cval);
+    else
+        block_reduce_kernel<double><<<grid_for(total, 128), 128, 0, st>>>((const double*)obj, s[0], s[1], (double*)out,
+            nb, ny, nx, cy, cx, fy, fx, ystep, xstep, op, skipna, cval);
+    return check_launch("block_reduce");
+}
+
+extern "C" int b200cs_block_upsample(const void* in, void* out, int elem_size, int64_t nb, int64_t cy,
+                                     int64_t cx, int fy, int fx, int y_staggered, int x_staggered,
+                                     void* stream) {
+    B200CS_REQUIRE(in && out, "block_upsample: NULL argument");
+    B200CS_REQUIRE(fy >= 1 && fx >= 1 && cy >= 1 && cx >= 1, "block_upsample: bad extents");
+    B200CS_REQUIRE(elem_size == 4 || elem_size == 8, "block_upsample: elem_size must be 4 or 8");
+    const int64_t ny = y_staggered ? (cy - 1) * fy + 1 : cy * fy;
+    const int64_t nx = x_staggered ? (cx - 1) * fx + 1 : cx * fx;
+    const int64_t total = nb * ny * nx;
+    if (total == 0) return B200CS_OK;
+    cudaStream_t st = as_stream(stream);
+    if (elem_size == 4)
+        upsample_kernel<uint32_t><<<grid_for(total, 256), 256, 0, st>>>((const uint32_t*)in, (uint32_t*)out, nb, cy, cx, ny, nx, fy, fx);
+    else
+        upsample_kernel<uint64_t><<<grid_for(total, 256), 256, 0, st>>>((const uint64_t*)in, (uint64_t*)out, nb, cy, cx, ny, nx, fy, fx);
+    return check_launch("block_upsample");
+}
+
+extern "C" int b200cs_gather_columns(const void* in, const int64_t s[2], void* out, int elem_size,
+                                     int64_t nb, int64_t ny, int64_t nx, int step, void* stream) {
+    B200CS_REQUIRE(in && out && s && step >= 1 && nx >= 1, "gather_columns: bad argument");
+    B200CS_REQUIRE(elem_size == 4 || elem_size == 8, "gather_columns: elem_size must be 4 or 8");
+    B200CS_REQUIRE(nb <= 65535, "gather_columns: nb > 65535");
+    const int64_t nlines = (nx - 1) / step + 1;
+    if (nb * ny * nlines == 0) return B200CS_OK;
+    dim3 grid((unsigned)((nlines + 31) / 32), (unsigned)((ny + 31) / 32), (unsigned)nb), block(32, 8);
+    cudaStream_t st = as_stream(stream);
+    if (elem_size == 4)
+        gather_columns_kernel<uint32_t><<<grid, block, 0, st>>>((const uint32_t*)in, s[0], s[1], (uint32_t*)out, nb, ny, nlines, step);
+    else
+        gather_columns_kernel<uint64_t><<<grid, block, 0, st>>>((const uint64_t*)in, s[0], s[1], (uint64_t*)out, nb, ny, nlines, step);
+    return check_launch("gather_columns");
+}
+
+extern "C" int b200cs_transpose_last2(const void* in, void* out, int elem_size, int64_t nb, int64_t ny,
+                                      int64_t nx, void* stream) {
+    const int64_t s[2] = {ny * nx, nx};
+    return b200cs_gather_columns(in, s, out, elem_size, nb, ny, nx, 1, stream);
+}
+
+extern "C" int b200cs_pressure_at_interface(const void* delp, int dtype, const int64_t s[2], void* out,
+                                            int64_t nb0, int64_t km, int64_t ncol, double toa, void* stream) {
+    B200CS_REQUIRE(delp && out && s && km >= 0, "pressure_at_interface: bad argument");
+    B200CS_REQUIRE(dtype == B200CS_F32 || dtype == B200CS_F64, "pressure_at_interface: dtype must be F32 or F64");
+    const int64_t total = nb0 * ncol;
+    if (total == 0) return B200CS_OK;
+    cudaStream_t st = as_stream(stream);
+    if (dtype == B200CS_F32)
+        pressure_interface_kernel<float><<<grid_for(total, 256), 256, 0, st>>>((const float*)delp, s[0], s[1], (float*)out, nb0, km, ncol, (float)toa);
+    else
+        pressure_interface_kernel<double><<<grid_for(total, 256), 256, 0, st>>>((const double*)delp, s[0], s[1], (double*)out, nb0, km, ncol, toa);
+    return check_launch("pressure_at_interface");
+}
+
+extern "C" int b200cs_mask_weights(const void* w, int w_dtype, const void* pc, const void* pf, int p_dtype,
+                                   void* out, int64_t nb0, int64_t km, int64_t ncol, int mode, void* stream) {
+    B200CS_REQUIRE(w && pc && pf && out, "mask_weights: NULL argument");
+    B200CS_REQUIRE(mode >= B200CS_MASK_NONE && mode <= B200CS_MASK_PFULL, "mask_weights: bad mask_mode");
+    const int64_t total = nb0 * km * ncol;
+    if (total == 0) return B200CS_OK;
+    cudaStream_t st = as_stream(stream);
+    const unsigned g = grid_for(total, 256);
+    if (w_dtype == B200CS_F32 && p_dtype == B200CS_F32)
+        mask_weights_kernel<float, float><<<g, 256, 0, st>>>((const float*)w, (const float*)pc, (const float*)pf, (float*)out, nb0, km, ncol, mode);
+    else if (w_dtype == B200CS_F32 && p_dtype == B200CS_F64)
+        mask_weights_kernel<float, double><<<g, 256, 0, st>>>((const float*)w, (const double*)pc, (const double*)pf, (float*)out, nb0, km, ncol, mode);
+    else if (w_dtype == B200CS_F64 && p_dtype == B200CS_F32)
+        mask_weights_kernel<double, float><<<g, 256, 0, st>>>((const double*)w, (const float*)pc, (const float*)pf, (double*)out, nb0, km, ncol, mode);
+    else if (w_dtype == B200CS_F64 && p_dtype == B200CS_F64)
+        mask_weights_kernel<double, double><<<g, 256, 0, st>>>((const double*)w, (const double*)pc, (const double*)pf, (double*)out, nb0, km, ncol, mode);
+    else
+        return set_err(B200CS_EINVAL, "mask_weights: dtype must be F32 or F64");
+    return check_launch("mask_weights");
+}

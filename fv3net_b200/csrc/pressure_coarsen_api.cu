@@ -1,0 +1,57 @@
+// pressure_coarsen_api.cu -- argument checking and dispatch of b200cs_pressure_coarsen
+#include "pressure_coarsen.cuh"
+
+namespace b200cs {
+int pc_entry_fx2_m0(const PcArgs&, int, int);
+int pc_entry_fx4_m0(const PcArgs&, int, int);
+int pc_entry_fx8_m0(const PcArgs&, int, int);
+int pc_entry_fx2_m1(const PcArgs&, int, int);
+int pc_entry_fx4_m1(const PcArgs&, int, int);
+int pc_entry_fx8_m1(const PcArgs&, int, int);
+}  // namespace b200cs
+
+using namespace b200cs;
+
+extern "C" int b200cs_pressure_coarsen(int nfields, const void* const* fields, int field_dtype,
+                                       const int64_t field_stride[3], const void* delp, int p_dtype,
+                                       const int64_t delp_stride[3], const void* w, int w_dtype,
+                                       const int64_t w_stride[2], void* const* out, void* delp_coarse,
+                                       int64_t nb0, int km, int64_t ny, int64_t nx, int fy, int fx,
+                                       double toa_pressure, int mask_mode, int iv, int kord, int mode,
+                                       void* stream) {
+    B200CS_REQUIRE(nfields >= 0 && nfields <= B200CS_MAX_FIELDS, "pressure_coarsen: nfields must be 0..%d", B200CS_MAX_FIELDS);
+    B200CS_REQUIRE(delp && w && delp_stride && w_stride, "pressure_coarsen: NULL argument");
+    B200CS_REQUIRE(nfields == 0 || (fields && out && field_stride), "pressure_coarsen: NULL field arrays");
+    for (int i = 0; i < nfields; i++) B200CS_REQUIRE(fields[i] && out[i], "pressure_coarsen: field %d is NULL", i);
+    B200CS_REQUIRE(fx == 2 || fx == 4 || fx == 8, "pressure_coarsen: fx must be 2, 4 or 8 (got %d)", fx);
+    B200CS_REQUIRE(fy == fx || fy == 1, "pressure_coarsen: fy must equal fx or be 1 (got %d)", fy);
+    B200CS_REQUIRE(nb0 >= 0 && nb0 <= 65535 && ny >= 1 && nx >= 1 && ny % fy == 0 && nx % fx == 0,
+                   "pressure_coarsen: extents must be multiples of the window");
+    B200CS_REQUIRE((ny + kTileY - 1) / kTileY <= 65535, "pressure_coarsen: ny too large");
+    B200CS_REQUIRE(km >= 4, "pressure_coarsen: km=%d; the PPM profile needs at least 4 levels", km);
+    B200CS_REQUIRE(mask_mode >= B200CS_MASK_NONE && mask_mode <= B200CS_MASK_PFULL, "pressure_coarsen: bad mask_mode");
+    B200CS_REQUIRE(mode == B200CS_EXACT || mode == B200CS_FAST, "pressure_coarsen: bad mode");
+    B200CS_REQUIRE((field_dtype | 1) == 1 && (p_dtype | 1) == 1 && (w_dtype | 1) == 1,
+                   "pressure_coarsen: dtypes must be F32 or F64");
+    if (kord > 6)
+        return set_err(B200CS_EUNSUPPORTED,
+                       "pressure_coarsen: kord=%d needs a two-sweep profile; use the unfused path (b200cs_mappm)", kord);
+    if (nb0 == 0) return B200CS_OK;
+    PcArgs a{nfields, fields, field_dtype, field_stride, delp, delp_stride, w, w_stride, out, delp_coarse,
+             nb0, km, ny, nx, fy, fx, toa_pressure, mask_mode, iv, kord, as_stream(stream)};
+    // with no fields the kernel still produces delp_coarse: run it on a dummy 1-field launch
+    const void* dummy_in[1] = {delp};
+    void* dummy_out[1] = {nullptr};
+    if (nfields == 0) {
+        return set_err(B200CS_EINVAL, "pressure_coarsen: nfields == 0 (use b200cs_weighted_block_average for delp)");
+    }
+    (void)dummy_in; (void)dummy_out;
+    if (mode == B200CS_EXACT) {
+        if (fx == 8) return pc_entry_fx8_m0(a, p_dtype, w_dtype);
+        if (fx == 4) return pc_entry_fx4_m0(a, p_dtype, w_dtype);
+        return pc_entry_fx2_m0(a, p_dtype, w_dtype);
+    }
+    if (fx == 8) return pc_entry_fx8_m1(a, p_dtype, w_dtype);
+    if (fx == 4) return pc_entry_fx4_m1(a, p_dtype, w_dtype);
+    return pc_entry_fx2_m1(a, p_dtype, w_dtype);
+}

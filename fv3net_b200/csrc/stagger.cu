@@ -1,0 +1,96 @@
+// stagger.cu -- K5: centre -> edge interpolation of a 6-tile cubed-sphere field with ghost
+// lines taken from the neighbouring faces.  Replaces xgcm 0.6.1 Grid.interp(delp, axis) built on
+// FV3_FACE_CONNECTIONS (external/vcm/vcm/cubedsphere/xgcm.py:7-34; call sites
+// external/vcm/vcm/cubedsphere/regridz.py:118-132 and coarsen_restarts.py:825-853).
+//
+//   out[j] = 0.5 * (ext[j-1] + ext[j]),  j = 0..n,   ext = tile padded by one ghost line a side
+//   left ghost  = LAST  line of the left  neighbour along ITS connecting axis
+//   right ghost = FIRST line of the right neighbour along ITS connecting axis
+//   a ghost line is index-reversed when the neighbour's axis differs from ours
+// (rule pinned bit-exactly against the reference's golden u, v: tests/test_oracle.py).
+//
+// Only lines 0, step, 2*step.. are produced when line_step > 1 (the D-grid pressure path keeps
+// only those, external/vcm/vcm/cubedsphere/coarsen.py:263-264), written compactly and, for the
+// x axis, line-major, so each kept line is contiguous.  Pure streaming: every needed input line
+// is read once, coalesced along the line.
+#include "common.cuh"
+
+namespace b200cs {
+
+// connection table: [tile][axis: 0=x,1=y][side: 0=left,1=right] -> {neighbour tile, neighbour axis}
+__constant__ int kConn[6][2][2][2] = {
+    {{{4, 1}, {1, 0}}, {{5, 1}, {2, 0}}},
+    {{{0, 0}, {3, 1}}, {{5, 0}, {2, 1}}},
+    {{{0, 1}, {3, 0}}, {{1, 1}, {4, 0}}},
+    {{{2, 0}, {5, 1}}, {{1, 0}, {4, 1}}},
+    {{{2, 1}, {5, 0}}, {{3, 1}, {0, 0}}},
+    {{{4, 0}, {1, 1}}, {{3, 0}, {0, 1}}},
+};
+
+// element `i` (position along the line) of interior/ghost line `j` in [-1, n] of tile t, level b1
+template <typename T>
+__device__ __forceinline__ T ext_at(const T* in, int64_t nb1, int64_t n, int t, int64_t b1, int axis_xy,
+                                    int64_t j, int64_t i) {
+    // axis_xy: 0 = lines are columns (stagger along x), 1 = lines are rows (stagger along y)
+    int tt = t;
+    int ax = axis_xy;
+    int64_t jj = j, ii = i;
+    if (j < 0 || j >= n) {
+        const int side = (j < 0) ? 0 : 1;
+        tt = kConn[t][axis_xy][side][0];
+        ax = kConn[t][axis_xy][side][1];
+        jj = (side == 0) ? n - 1 : 0;
+        if (ax != axis_xy) ii = n - 1 - i;
+    }
+    const T* base = in + ((int64_t)tt * nb1 + b1) * n * n;
+    // ax == 0: line index is the x coordinate, position runs along y
+    return (ax == 0) ? base[ii * n + jj] : base[jj * n + ii];
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+stagger_kernel(const T* __restrict__ in, T* __restrict__ out, int64_t nb1, int64_t n, int axis, int step) {
+    // axis: 0 = y (lines are rows), 1 = x (lines are columns)
+    const int axis_xy = (axis == 0) ? 1 : 0;
+    const int64_t nlines = n / step + 1;
+    const int64_t total = 6 * nb1 * nlines * n;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        int64_t i, l;
+        if (axis == 0 || step > 1) {  // line-major output [.., nlines, n]
+            i = idx % n;
+            l = (idx / n) % nlines;
+        } else {  // full x-stagger keeps the natural [.., n, n+1] layout
+            l = idx % nlines;
+            i = (idx / nlines) % n;
+        }
+        const int64_t b1 = (idx / (n * nlines)) % nb1;
+        const int t = (int)(idx / (n * nlines * nb1));
+        const int64_t j = l * step;
+        const T a = ext_at(in, nb1, n, t, b1, axis_xy, j - 1, i);
+        const T b = ext_at(in, nb1, n, t, b1, axis_xy, j, i);
+        out[idx] = T(0.5) * (a + b);
+    }
+}
+
+}  // namespace b200cs
+
+using namespace b200cs;
+
+extern "C" int b200cs_stagger(const void* in, void* out, int dtype, int64_t nb1, int64_t n, int axis,
+                              int line_step, void* stream) {
+    B200CS_REQUIRE(in && out, "stagger: NULL argument");
+    B200CS_REQUIRE(axis == 0 || axis == 1, "stagger: axis must be 0 (y) or 1 (x)");
+    B200CS_REQUIRE(line_step >= 1 && n >= 1 && n % line_step == 0, "stagger: line_step must divide n");
+    B200CS_REQUIRE(dtype == B200CS_F32 || dtype == B200CS_F64, "stagger: dtype must be F32 or F64");
+    const int64_t total = 6 * nb1 * (n / line_step + 1) * n;
+    if (total == 0) return B200CS_OK;
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > 148LL * 32) blocks = 148LL * 32;
+    cudaStream_t st = as_stream(stream);
+    if (dtype == B200CS_F32)
+        stagger_kernel<float><<<(unsigned)blocks, 256, 0, st>>>((const float*)in, (float*)out, nb1, n, axis, line_step);
+    else
+        stagger_kernel<double><<<(unsigned)blocks, 256, 0, st>>>((const double*)in, (double*)out, nb1, n, axis, line_step);
+    return check_launch("stagger");
+}

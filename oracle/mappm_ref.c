@@ -31,7 +31,7 @@
  *     with return code -1.
  *
  * MIN/MAX follow gfortran's inline expansion (ignore a NaN operand when the other is
- * a number), which is fminf/fmaxf.  SIGN(a,b) = copysignf(|a|,b).
+ * a number), which is fminf/fmaxf.  SIGN(a,b) = copysignf(|a|,b), with a NaN b taken as positive.
  */
 #include <math.h>
 #include <stdlib.h>
@@ -44,7 +44,9 @@ static inline float min2(float a, float b) { return fminf(a, b); }
 static inline float max2(float a, float b) { return fmaxf(a, b); }
 static inline float min3(float a, float b, float c) { return fminf(fminf(a, b), c); }
 static inline float max3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
-static inline float sgn(float a, float b) { return copysignf(fabsf(a), b); }
+/* SIGN(a,b); a NaN b counts as positive (gfortran copies b's sign BIT, which for a NaN depends on
+ * how the NaN arose and on the platform -- defined here so that CPU and GPU agree) */
+static inline float sgn(float a, float b) { return (b != b) ? fabsf(a) : copysignf(fabsf(a), b); }
 
 /* 1-based accessors onto per-column arrays of length km (or km+1) */
 #define A1(k) a1_[(k)-1]
