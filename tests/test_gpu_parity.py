@@ -327,7 +327,7 @@ def test_pressure_coarsen_exact_vs_oracle(core, oracle, f, n, pdt, mask_mode):
     got, dco = core.pressure_coarsen(fields, delp, w, f, 300.0, mask_mode=mask_mode)
     exp, edco = _oracle_pressure(oracle, fields, delp, w, f, mask_mode)
     assert eq(dco, edco)
-    if mask_mode == "phalf":
+    if mask_mode == "phalf" and n >= 40:  # the 8x8 case is too smooth to bury a whole coarse cell
         assert np.isnan(exp[0]).any(), "test should exercise fully masked coarse cells"
     for g, e in zip(got, exp):
         assert eq(g, e)
