@@ -8,6 +8,8 @@ int pc_entry_fx8_m0(const PcArgs&, int, int);
 int pc_entry_fx2_m1(const PcArgs&, int, int);
 int pc_entry_fx4_m1(const PcArgs&, int, int);
 int pc_entry_fx8_m1(const PcArgs&, int, int);
+bool pc_fast_covers(const PcArgs&, int, int, int);
+int pc_fast_entry(const PcArgs&);
 }  // namespace b200cs
 
 using namespace b200cs;
@@ -51,6 +53,8 @@ extern "C" int b200cs_pressure_coarsen(int nfields, const void* const* fields, i
         if (fx == 4) return pc_entry_fx4_m0(a, p_dtype, w_dtype);
         return pc_entry_fx2_m0(a, p_dtype, w_dtype);
     }
+    // the specialised kernel (fp32, 8-wide windows, kord <= 3); everything else: generic kernel + FMA
+    if (pc_fast_covers(a, field_dtype, p_dtype, w_dtype)) return pc_fast_entry(a);
     if (fx == 8) return pc_entry_fx8_m1(a, p_dtype, w_dtype);
     if (fx == 4) return pc_entry_fx4_m1(a, p_dtype, w_dtype);
     return pc_entry_fx2_m1(a, p_dtype, w_dtype);

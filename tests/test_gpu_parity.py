@@ -294,7 +294,9 @@ def _oracle_pressure(oracle, fields, delp, w, f, mask_mode, edge_lines=False):
         up = np.repeat(delp_c, f, axis=-1)
     else:
         delp_c = oracle.weighted_block_average(delp, w4, f)
-        up = oracle.block_upsample(delp_c, f)
+        # plain repeat: the reference's block_upsample reads an odd coarse extent (n=40, f=8 -> 5)
+        # as an interface axis, a quirk of its API that the fused path does not go through
+        up = np.repeat(np.repeat(delp_c, f, axis=-1), f, axis=-2)
     phalf_c = oracle.pressure_at_interface(up, 300.0)
     phalf_f = oracle.pressure_at_interface(delp, 300.0)
     outs = []
@@ -303,6 +305,7 @@ def _oracle_pressure(oracle, fields, delp, w, f, mask_mode, edge_lines=False):
     else:
         pfull = oracle.pressure_at_midpoint_log(up, 300.0)
         mw = oracle.mask_weights(w4, pfull, phalf_c, phalf_f, extrapolate=(mask_mode == "pfull"))
+        _oracle_pressure.masked_fraction = float((mw == 0).mean())
     for x in fields:
         r = oracle.regrid_vertical(phalf_f, x, phalf_c, nthreads=8)
         if edge_lines:
@@ -327,8 +330,8 @@ def test_pressure_coarsen_exact_vs_oracle(core, oracle, f, n, pdt, mask_mode):
     got, dco = core.pressure_coarsen(fields, delp, w, f, 300.0, mask_mode=mask_mode)
     exp, edco = _oracle_pressure(oracle, fields, delp, w, f, mask_mode)
     assert eq(dco, edco)
-    if mask_mode == "phalf" and n >= 40:  # the 8x8 case is too smooth to bury a whole coarse cell
-        assert np.isnan(exp[0]).any(), "test should exercise fully masked coarse cells"
+    if mask_mode == "phalf":
+        assert _oracle_pressure.masked_fraction > 0.01, "test should exercise below-surface masking"
     for g, e in zip(got, exp):
         assert eq(g, e)
 
@@ -379,22 +382,65 @@ def test_pressure_coarsen_kord_iv_and_errors(core, oracle):
         core.pressure_coarsen([x[:, :3]], delp[:, :3], w, f)
 
 
-def test_pressure_coarsen_fast_mode_tolerance(core, oracle):
-    """FAST (FMA) mode vs EXACT: within 1e-6 of the field scale (north star tolerance)."""
-    rng = np.random.default_rng(99)
-    nb, km, n, f = 6, 79, 48, 8
-    delp = _synthetic_columns(rng, nb, km, n, np.float32)
-    w = rng.uniform(3.6e8, 8.3e8, size=(nb, n, n)).astype(np.float32)
-    fields = [rng.uniform(180, 320, size=(nb, km, n, n)).astype(np.float32),
-              (rng.normal(size=(nb, km, n, n)) * 10).astype(np.float32)]
-    ex, _ = core.pressure_coarsen(fields, delp, w, f, mode=core.EXACT)
-    fa, _ = core.pressure_coarsen(fields, delp, w, f, mode=core.FAST)
+def _fast_vs_exact(core, fields, delp, w, f, rtol=1e-6, **kw):
+    """FAST must reproduce EXACT (itself bit-checked against the oracle) within rtol of the field
+    scale, with identical NaN patterns and a bit-identical coarse delp (the mask chain)."""
+    ex, dce = core.pressure_coarsen(fields, delp, w, f, mode=core.EXACT, **kw)
+    fa, dcf = core.pressure_coarsen(fields, delp, w, f, mode=core.FAST, **kw)
+    if dce is not None:
+        assert eq(dce, dcf)
+    worst = 0.0
     for a, b, x in zip(ex, fa, fields):
         assert np.array_equal(np.isnan(a), np.isnan(b))
-        scale = np.abs(x).max()
-        err = np.nanmax(np.abs(a - b)) / scale
-        print(f"FAST vs EXACT max |diff| / scale = {err:.3e}")
-        assert err <= 1e-6
+        scale = np.nanmax(np.abs(x))
+        err = np.nanmax(np.abs(a.astype(np.float64) - b.astype(np.float64))) / scale
+        worst = max(worst, err)
+        assert err <= rtol, err
+    return worst
+
+
+@pytest.mark.parametrize("nfields", [1, 2, 4, 5, 7])
+@pytest.mark.parametrize("n", [48, 40, 64])
+def test_pressure_coarsen_fast_mode_tolerance(core, oracle, nfields, n):
+    """The specialised FAST kernel (fp32, f=8, kord<=3) vs EXACT: within 1e-6 of the field scale
+    (north star tolerance); n=40 exercises partially filled 32-column tiles."""
+    rng = np.random.default_rng(99 + n + nfields)
+    nb, km, f = 6, 79, 8
+    delp = _synthetic_columns(rng, nb, km, n, np.float32)
+    w = rng.uniform(3.6e8, 8.3e8, size=(nb, n, n)).astype(np.float32)
+    scales = [None, 10.0, 1e-3, 10.0, 3.0, 250.0, 1.0]
+    fields = []
+    for s in scales[:nfields]:
+        if s is None:
+            fields.append(rng.uniform(180, 320, size=(nb, km, n, n)).astype(np.float32))
+        else:
+            fields.append((rng.normal(size=(nb, km, n, n)) * s).astype(np.float32))
+    if nfields >= 2:
+        fields[1] = sprinkle_nans(rng, fields[1], 0.002)
+    for mask_mode in ("phalf", "none"):
+        worst = _fast_vs_exact(core, fields, delp, w, f, mask_mode=mask_mode)
+        print(f"FAST vs EXACT nf={nfields} n={n} {mask_mode}: max |diff| / scale = {worst:.3e}")
+
+
+def test_pressure_coarsen_fast_smooth_fields_and_options(core, oracle):
+    """smooth (realistic) profiles, every iv, pfull mask, NaN weights, edge lines"""
+    rng = np.random.default_rng(5)
+    nb, km, n, f = 3, 33, 64, 8
+    delp = _synthetic_columns(rng, nb, km, n, np.float32)
+    w = rng.uniform(0.5, 1.0, size=(nb, n, n)).astype(np.float32)
+    z = np.linspace(0, 1, km)[None, :, None, None]
+    T = (210 + 80 * z ** 2 + rng.normal(0, 0.5, size=(nb, km, n, n))).astype(np.float32)
+    qv = (1e-2 * np.exp(-6 * (1 - z)) * rng.uniform(0.5, 1.5, size=(nb, km, n, n))).astype(np.float32)
+    for iv in (-2, -1, 0, 1, 2):
+        _fast_vs_exact(core, [T, qv], delp, w, f, iv=iv, kord=3)
+    _fast_vs_exact(core, [T, qv], delp, w, f, mask_mode="pfull")
+    w2 = w.copy()
+    w2[0, 3, 5] = np.nan
+    w2[1, 8:16, 8:16] = np.nan
+    _fast_vs_exact(core, [T, qv], delp, w2, f)
+    nl = 9
+    wl = rng.uniform(0.5, 1.0, size=(nb, nl, n)).astype(np.float32)
+    _fast_vs_exact(core, [T[:, :, :nl] * 0.1], delp[:, :, :nl], wl, f, edge_lines=True, return_delp_coarse=False)
 
 
 # ------------------------------------------------------------------------------------------
