@@ -13,6 +13,7 @@ F32, F64 = 0, 1
 OP_SUM, OP_MEAN, OP_MIN, OP_MAX, OP_MEDIAN, OP_MODE = range(6)
 MASK_NONE, MASK_PHALF, MASK_PFULL = 0, 1, 2
 EXACT, FAST = 0, 1
+SEQ_WINDOW = 2
 MAX_FIELDS = 16
 
 EXPORTS = [

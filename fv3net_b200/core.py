@@ -321,7 +321,7 @@ def mask_weights(weights, p_coarse_on_fine, phalf_fine, mask_mode="phalf"):
 
 
 def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.0, mask_mode="phalf",
-                     edge_lines=False, iv=1, kord=1, mode=EXACT, return_delp_coarse=True):
+                     edge_lines=False, iv=1, kord=1, mode=EXACT, return_delp_coarse=True, seq_window=False):
     """Fused pressure-level coarse-graining (one pass over the fine data).
 
     Equivalent to regrid_to_area_weighted_pressure + weighted_block_average with the masked
@@ -331,6 +331,8 @@ def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.
 
     fields: list of ``[B, km, ny, nx]`` arrays (B = tiles); delp same shape; weights ``[B, ny, nx]``.
     edge_lines: windows are 1 x f (the rows are the kept lines of a D-grid wind component).
+    seq_window: the window axis was not the contiguous axis of the reference's arrays (v lines are
+    gathered columns), so sums follow numpy's sequential order for strided reductions.
     Returns (list of coarse fields ``[B, km, cy, cx]``, coarse delp or None)."""
     f = int(coarsening_factor)
     was_np = not isinstance(delp, torch.Tensor)
@@ -371,7 +373,7 @@ def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.
         len(fs), _lib.ptrarr([x.data_ptr() for x in fs]), _DT[fdt], _lib.i64arr(fs[0].stride()[:3] if fs else (0, 0, 0)),
         d.data_ptr(), _DT[d.dtype], _lib.i64arr(d.stride()[:3]), w.data_ptr(), _DT[wdt], _lib.i64arr(w.stride()[:2]),
         _lib.ptrarr([o.data_ptr() for o in outs]), dco.data_ptr() if dco is not None else None,
-        nb0, km, ny, nx, fy, f, float(toa_pressure), _MASK[mask_mode], int(iv), int(kord), int(mode), _stream())
+        nb0, km, ny, nx, fy, f, float(toa_pressure), _MASK[mask_mode], int(iv), int(kord), int(mode) | (_lib.SEQ_WINDOW if seq_window else 0), _stream())
     _lib.check(rc, "pressure_coarsen")
     if was_np:
         return [o.cpu().numpy() for o in outs], (dco.cpu().numpy() if dco is not None else None)

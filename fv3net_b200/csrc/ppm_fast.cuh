@@ -15,19 +15,21 @@
 //     max3(0,d01,-d12): identical values (rounding is monotone), two subtractions fewer;
 //   * ONE call site of advance() inside the per-output-layer loop: lanes of a warp that sit on
 //     different source layers stay converged (the exact machine has three);
-//   * level data is fetched one source layer ahead into registers (Acc::fetch) so that the load
-//     latency is covered by a whole layer of arithmetic.
+//   * level data arrives through the accessor's fetch(), which the fused kernel backs with a
+//     per-thread cp.async ring in shared memory several source layers deep (a register prefetch
+//     ends up as a phi copy that waits for the load inside the same iteration).
 // Every level-search and mask decision is made on the same fp32 pressures as the reference
 // (sequential cumsum), so which source layers feed which output layer is identical; only the
 // rounding of the parabola coefficients and integrals differs (a few ulp; tests state 1e-6).
 //
-// Accessor concept (stateful, sequential):
-//   void  fetch(int jq, int jpe)   issue loads of q[.][min(jq,km-1)] and of the datum that
-//                                  defines edge pe[min(jpe,km)] into the accessor's registers
-//   float q(int f)                 the fetched layer mean of field f
-//   float pe(float prev)           the fetched edge pressure given the previous edge
+// Accessor concept (stateful; levels are requested in increasing order, one at a time):
+//   void  fetch(int jq, int jpe)   make q[.][min(jq,km-1)] and the datum that defines edge
+//                                  pe[min(jpe,km)] current
+//   float q(int f)                 the current layer mean of field f
+//   float pe(float prev)           the current edge pressure given the previous edge
 //                                  (prev + delp for a cumsum source, or the stored edge itself)
 //   float pe0()                    edge 0
+//   void  rewind()                 the next fetch() returns the current level once more
 #pragma once
 #include "ppm_stream.cuh"
 
@@ -105,7 +107,7 @@ struct PpmFast {
         const float p4 = a.pe(p3);
 #pragma unroll
         for (int f = 0; f < NF; f++) qD[f] = a.q(f);
-        // the accessor now holds q[3] and the datum of pe[4]: the first advance consumes them
+        a.rewind();  // the first advance needs q[3] and pe[4] again
         pe_top = p0;
         const float d1 = p1 - p0, d2 = p2 - p1, d3 = p3 - p2, d4 = p4 - p3;
         float s2[NF], s3[NF], e3[NF], dc0[NF], x1v[NF];
@@ -197,6 +199,7 @@ struct PpmFast {
         const float dpm = dp0;
         dp0 = dp1; dp1 = dp2;
         pe_lo = pe_hi; pe_hi = pe_b; pe_b = pe_a;
+        a.fetch(Ln + 2, Ln + 3);
         const float pe_n = a.pe(pe_a);   // pe[Ln+3] (garbage beyond the surface, unused)
         dp2 = pe_n - pe_a;
         pe_a = pe_n;
@@ -208,7 +211,6 @@ struct PpmFast {
             q0[f] = q1[f]; q1[f] = q2[f]; q2[f] = a.q(f);
             dl[f] = e1[f]; dm[f] = dc1[f];
         }
-        a.fetch(Ln + 3, Ln + 4);
         if (Ln + 1 <= km - 2) {
             // layer Ln+1 has a centred slope and interface Ln+1 an interior edge value
             const float Pm0 = dpm + dp0, P01 = dp0 + dp1, P12 = dp1 + dp2;

@@ -37,9 +37,11 @@ struct FieldPtrs {
 
 // numpy order along a window row held by FX adjacent lanes: FX==8 -> pairwise tree
 // ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)); FX<8 -> sequential from 0 (numpy pairwise_sum, n<8)
+// seq: the window axis was NOT the contiguous axis of the reference's array (D-grid v lines are
+// gathered columns): numpy then adds the FX elements one after the other onto 0.
 template <int FX, typename T>
-__device__ __forceinline__ T row_reduce(T v, int lane) {
-    if (FX == 8) {
+__device__ __forceinline__ T row_reduce(T v, int lane, bool seq = false) {
+    if (FX == 8 && !seq) {
         v = v + __shfl_xor_sync(0xffffffffu, v, 1);
         v = v + __shfl_xor_sync(0xffffffffu, v, 2);
         v = v + __shfl_xor_sync(0xffffffffu, v, 4);
@@ -80,7 +82,8 @@ pressure_coarsen_kernel(FieldPtrs<NF> fp, int field_f64, int64_t fs0, int64_t fs
                         const TP* __restrict__ delp, int64_t ds0, int64_t dsl, int64_t dsy,
                         const TW* __restrict__ w, int64_t ws0, int64_t wsy,
                         typename Promote<TP, TW>::type* __restrict__ delp_coarse, int km, int64_t ny,
-                        int64_t nx, int fy, double toa, int mask_mode, int iv, int kord) {
+                        int64_t nx, int fy, double toa, int mask_mode, int iv, int kord, int seq_i) {
+    const bool seq = seq_i != 0;
     using TC = typename Promote<TP, TW>::type;  // dtype of coarse delp / coarse pressures
     constexpr int CW = kTileX / FX;             // cells per tile row
     const int CH = kTileY / fy;                 // cell rows per tile
@@ -110,7 +113,7 @@ pressure_coarsen_kernel(FieldPtrs<NF> fp, int field_f64, int64_t fs0, int64_t fs
     // ---------------- Phase A: pressures -------------------------------------------------
     const TW wv = active ? w[b0 * ws0 + y * wsy + x] : TW(0);
     {   // weight sum per cell (2-D weights: one value per cell), numpy order
-        TW rs = row_reduce<FX>(nan_to_zero(wv), lane);
+        TW rs = row_reduce<FX>(nan_to_zero(wv), lane, seq);
         if ((lane & (FX - 1)) == 0) s_part[ty * CW + lane / FX] = rs;
         __syncthreads();
         if (tid < ncell) {
@@ -135,7 +138,7 @@ pressure_coarsen_kernel(FieldPtrs<NF> fp, int field_f64, int64_t fs0, int64_t fs
             if (k0 + kk < km) {
                 pacc = pacc + nan_to_zero(d[kk]);  // xarray cumsum == nancumsum
                 s_pe1[(k0 + kk + 1) * kThreads + tid] = (float)pacc;
-                TC rs = row_reduce<FX>(nan_to_zero((TC)d[kk] * (TC)wv), lane);
+                TC rs = row_reduce<FX>(nan_to_zero((TC)d[kk] * (TC)wv), lane, seq);
                 if ((lane & (FX - 1)) == 0) s_rowsA[((buf * kKC + kk) * kTileY + ty) * CW + lane / FX] = rs;
             }
         }
@@ -213,10 +216,10 @@ pressure_coarsen_kernel(FieldPtrs<NF> fp, int field_f64, int64_t fs0, int64_t fs
                 TW* dst = s_part + (size_t)((buf * kKC + kk) * kTileY + ty) * CW * (NF + 1) + (lane / FX) * (NF + 1);
 #pragma unroll
                 for (int i = 0; i < NF; i++) {
-                    TW rs = row_reduce<FX>(nan_to_zero((TW)o[i] * wk), lane);
+                    TW rs = row_reduce<FX>(nan_to_zero((TW)o[i] * wk), lane, seq);
                     if ((lane & (FX - 1)) == 0) dst[i] = rs;
                 }
-                TW rd = row_reduce<FX>(nan_to_zero(wk), lane);
+                TW rd = row_reduce<FX>(nan_to_zero(wk), lane, seq);
                 if ((lane & (FX - 1)) == 0) dst[NF] = rd;
             }
         }
@@ -270,6 +273,7 @@ struct PcArgs {
     double toa;
     int mask_mode, iv, kord;
     cudaStream_t st;
+    int seq;  // B200CS_SEQ_WINDOW
 };
 
 template <int MODE, int NF, typename TP, typename TW, int FX>
@@ -289,7 +293,7 @@ int launch_pc(const PcArgs& a, int first) {
     kern<<<grid, kThreads, smem, a.st>>>(fp, a.field_dtype == B200CS_F64, a.fstride[0], a.fstride[1], a.fstride[2],
                                          (const TP*)a.delp, a.dstride[0], a.dstride[1], a.dstride[2], (const TW*)a.w,
                                          a.wstride[0], a.wstride[1], first == 0 ? (TC*)a.delp_coarse : nullptr, a.km,
-                                         a.ny, a.nx, a.fy, a.toa, a.mask_mode, a.iv, a.kord);
+                                         a.ny, a.nx, a.fy, a.toa, a.mask_mode, a.iv, a.kord, a.seq);
     return check_launch("pressure_coarsen");
 }
 

@@ -32,7 +32,9 @@ extern "C" int b200cs_pressure_coarsen(int nfields, const void* const* fields, i
     B200CS_REQUIRE((ny + kTileY - 1) / kTileY <= 65535, "pressure_coarsen: ny too large");
     B200CS_REQUIRE(km >= 4, "pressure_coarsen: km=%d; the PPM profile needs at least 4 levels", km);
     B200CS_REQUIRE(mask_mode >= B200CS_MASK_NONE && mask_mode <= B200CS_MASK_PFULL, "pressure_coarsen: bad mask_mode");
-    B200CS_REQUIRE(mode == B200CS_EXACT || mode == B200CS_FAST, "pressure_coarsen: bad mode");
+    B200CS_REQUIRE((mode & ~(B200CS_FAST | B200CS_SEQ_WINDOW)) == 0, "pressure_coarsen: bad mode");
+    const int seq = (mode & B200CS_SEQ_WINDOW) ? 1 : 0;
+    mode &= B200CS_FAST;
     B200CS_REQUIRE((field_dtype | 1) == 1 && (p_dtype | 1) == 1 && (w_dtype | 1) == 1,
                    "pressure_coarsen: dtypes must be F32 or F64");
     if (kord > 6)
@@ -40,7 +42,7 @@ extern "C" int b200cs_pressure_coarsen(int nfields, const void* const* fields, i
                        "pressure_coarsen: kord=%d needs a two-sweep profile; use the unfused path (b200cs_mappm)", kord);
     if (nb0 == 0) return B200CS_OK;
     PcArgs a{nfields, fields, field_dtype, field_stride, delp, delp_stride, w, w_stride, out, delp_coarse,
-             nb0, km, ny, nx, fy, fx, toa_pressure, mask_mode, iv, kord, as_stream(stream)};
+             nb0, km, ny, nx, fy, fx, toa_pressure, mask_mode, iv, kord, as_stream(stream), seq};
     // with no fields the kernel still produces delp_coarse: run it on a dummy 1-field launch
     const void* dummy_in[1] = {delp};
     void* dummy_out[1] = {nullptr};

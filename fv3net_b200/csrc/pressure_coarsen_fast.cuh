@@ -29,23 +29,51 @@ namespace b200cs {
 constexpr int kFastKA = 8;  // Phase A levels per barrier
 constexpr int kFastKC = 4;  // Phase B levels per barrier
 
+constexpr int kRing = 4;  // cp.async ring depth (levels): kRing-1 levels in flight per thread
+
+__device__ __forceinline__ void cp_async4(unsigned smem_addr, const void* gptr) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_addr), "l"(gptr) : "memory");
+}
+
+// Level source of one thread's column: NF field values + delp per level, streamed global ->
+// shared with cp.async into a private ring (slot = level mod kRing) kRing-1 levels ahead of use.
+// No registers are tied up by data in flight and nothing waits on a load in the iteration that
+// issued it.
 template <int NF>
 struct FastSrc {
     const char* f[NF];
     const char* delp;
-    unsigned off_q, off_d;    // byte offsets of the NEXT level to fetch (this thread's column)
+    unsigned off_q, off_d;    // byte offsets of the next level to ISSUE (this thread's column)
     unsigned step_q, step_d;  // level strides in bytes
-    int j, km;                // next level index to fetch
+    int ji, jc, km;           // next level to issue / level made current by the last fetch()
+    unsigned ring;            // shared-space address of this thread's element of slot 0, value 0
     float toa;
     float qv[NF], dv;
-    // the machine asks for (jq_, jpe_) in strictly increasing order, one level at a time
-    __device__ __forceinline__ void fetch(int jq_, int jpe_) {
-        (void)jq_; (void)jpe_;
+    static constexpr unsigned kValStride = kThreads * 4, kSlotStride = (NF + 1) * kThreads * 4;
+    __device__ __forceinline__ void issue() {
+        const unsigned dst = ring + (unsigned)(ji & (kRing - 1)) * kSlotStride;
 #pragma unroll
-        for (int i = 0; i < NF; i++) qv[i] = __ldg((const float*)(f[i] + off_q));
-        dv = __ldg((const float*)(delp + off_d));
-        if (j < km - 1) { off_q += step_q; off_d += step_d; j++; }
+        for (int i = 0; i < NF; i++) cp_async4(dst + i * kValStride, f[i] + off_q);
+        cp_async4(dst + NF * kValStride, delp + off_d);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        if (ji < km - 1) { off_q += step_q; off_d += step_d; }  // beyond the surface: re-issue the last level
+        ji++;
     }
+    __device__ __forceinline__ void prologue() {
+#pragma unroll
+        for (int i = 0; i < kRing - 1; i++) issue();
+    }
+    // levels are requested in increasing order, one at a time (the arguments document which)
+    __device__ __forceinline__ void fetch(int, int) {
+        jc++;
+        if (ji < jc + kRing) issue();  // level jc+kRing-1 replaces the slot of level jc-1; false only right after rewind()
+        asm volatile("cp.async.wait_group %0;" ::"n"(kRing - 1) : "memory");
+        const unsigned src = ring + (unsigned)(jc & (kRing - 1)) * kSlotStride;
+#pragma unroll
+        for (int i = 0; i < NF; i++) asm volatile("ld.shared.f32 %0, [%1];" : "=f"(qv[i]) : "r"(src + i * kValStride));
+        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(dv) : "r"(src + NF * kValStride));
+    }
+    __device__ __forceinline__ void rewind() { jc--; }
     __device__ __forceinline__ float q(int i) const { return qv[i]; }
     __device__ __forceinline__ float pe(float prev) const { return prev + nan_to_zero(dv); }
     __device__ __forceinline__ float pe0() const { return toa; }
@@ -80,8 +108,17 @@ __device__ __forceinline__ float reduce_fields8(const float (&v)[NF], int lane) 
         return t + __shfl_xor_sync(m, t, 4);
     }
 }
-__device__ __forceinline__ float reduce_row8(float t) {
+// seq: numpy's order for a window whose elements were strided in the reference's array
+// (sequential onto 0) -- keeps the coarse delp, hence the mask, bit-identical for D-grid v lines
+__device__ __forceinline__ float reduce_row8(float t, bool seq = false, int lane = 0) {
     const unsigned m = 0xffffffffu;
+    if (seq) {
+        const int base = lane & ~7;
+        float r = 0.f;
+#pragma unroll
+        for (int c = 0; c < 8; c++) r = r + __shfl_sync(m, t, base + c);
+        return r;
+    }
     t = t + __shfl_xor_sync(m, t, 1);
     t = t + __shfl_xor_sync(m, t, 2);
     return t + __shfl_xor_sync(m, t, 4);
@@ -99,8 +136,9 @@ pressure_coarsen_fast_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_t
                              const float* __restrict__ delp, int64_t ds0, int64_t dsl, int64_t dsy,
                              const float* __restrict__ w, int64_t ws0, int64_t wsy,
                              float* __restrict__ delp_coarse, int km, int64_t ny, int64_t nx, float toa,
-                             int mask_mode, int iv) {
+                             int mask_mode, int iv, int seq_i) {
     constexpr int FX = 8;
+    const bool seq = seq_i != 0;
     constexpr int CW = kTileX / FX;   // cells per tile row
     constexpr int CH = kTileY / FY;   // cell rows per tile
     constexpr int NCELL = CW * CH;
@@ -118,10 +156,11 @@ pressure_coarsen_fast_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_t
     float* s_rows = reinterpret_cast<float*>(s_lvl + (size_t)NCELL * km);      // [2][KA][8][CW]
     float* s_part = s_rows + 2 * kFastKA * kTileY * CW;                        // [2][KC][8][CW][NF+1]
     float* s_den = s_part + 2 * kFastKC * kTileY * CW * (NF + 1);              // [NCELL]
+    float* s_ring = s_den + ((NCELL + 3) & ~3);                                // [kRing][NF+1][256]
 
     // ---------------- Phase A: coarse pressure levels of the tile's cells -------------------
     const float wv = active ? __ldg(w + b0 * ws0 + y * wsy + x) : 0.f;
-    const float wrow = reduce_row8(nan_to_zero(wv));  // weight sum of this window row
+    const float wrow = reduce_row8(nan_to_zero(wv), seq, lane);  // weight sum of this window row
     if ((lane & (FX - 1)) == 0) s_part[ty * CW + lane / FX] = wrow;
     __syncthreads();
     if (tid < NCELL) {
@@ -143,7 +182,7 @@ pressure_coarsen_fast_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_t
         for (int kk = 0; kk < kFastKA; kk++) {
             if (k0 + kk < km) {
                 pacc = pacc + nan_to_zero(d[kk]);  // xarray cumsum == nancumsum
-                const float rs = reduce_row8(nan_to_zero(d[kk] * wv));
+                const float rs = reduce_row8(nan_to_zero(d[kk] * wv), seq, lane);
                 if ((lane & (FX - 1)) == 0) s_rows[((buf * kFastKA + kk) * kTileY + ty) * CW + lane / FX] = rs;
             }
         }
@@ -185,8 +224,10 @@ pressure_coarsen_fast_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_t
         src.delp = (const char*)dcol;
         src.off_q = 0; src.off_d = 0;
         src.step_q = (unsigned)(fsl * 4); src.step_d = (unsigned)(dsl * 4);
-        src.j = 0; src.km = km;
+        src.ji = 0; src.jc = -1; src.km = km;
+        src.ring = (unsigned)__cvta_generic_to_shared(s_ring + tid);
         src.toa = toa;
+        src.prologue();
     }
     PpmFast<NF> st;
     st.init(src, km, iv, psurf);
@@ -215,7 +256,7 @@ pressure_coarsen_fast_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_t
                 float* dst = s_part + (size_t)((buf * kFastKC + kk) * kTileY + ty) * CW * (NF + 1) + (lane / FX) * (NF + 1);
                 if (writer) dst[own] = tot;
                 float rd = wrow;
-                if (!__all_sync(0xffffffffu, keep)) rd = reduce_row8(nan_to_zero(wk));
+                if (!__all_sync(0xffffffffu, keep)) rd = reduce_row8(nan_to_zero(wk), seq, lane);
                 if (den_writer) dst[NF] = rd;
             }
         }
@@ -244,7 +285,8 @@ template <int NF, int FY>
 size_t pressure_coarsen_fast_smem(int km) {
     constexpr int CW = kTileX / 8, NCELL = CW * (kTileY / FY);
     return (size_t)NCELL * km * sizeof(float4) +
-           sizeof(float) * (2 * kFastKA * kTileY * CW + 2 * kFastKC * kTileY * CW * (NF + 1) + NCELL);
+           sizeof(float) * (2 * kFastKA * kTileY * CW + 2 * kFastKC * kTileY * CW * (NF + 1) + ((NCELL + 3) & ~3) +
+                            kRing * (NF + 1) * kThreads);
 }
 
 template <int NF, int FY>
@@ -261,7 +303,7 @@ int launch_pc_fast(const PcArgs& a, int first) {
     kern<<<grid, kThreads, smem, a.st>>>(fp, a.fstride[0], a.fstride[1], a.fstride[2], (const float*)a.delp,
                                          a.dstride[0], a.dstride[1], a.dstride[2], (const float*)a.w, a.wstride[0],
                                          a.wstride[1], first == 0 ? (float*)a.delp_coarse : nullptr, a.km, a.ny, a.nx,
-                                         (float)a.toa, a.mask_mode, a.iv);
+                                         (float)a.toa, a.mask_mode, a.iv, a.seq);
     return check_launch("pressure_coarsen(fast)");
 }
 

@@ -169,7 +169,7 @@ def _edge_pressure(u, delp, length, toa_pressure, f, edge, mask_mode, mode):
         v_lines = core.gather_columns(u4, f)                      # [6, z, n/f+1, n]
         w_lines = core.gather_columns(length, f)                  # [6, n/f+1, n]
         outs, _ = core.pressure_coarsen([v_lines], delp_lines, w_lines, f, toa_pressure, mask_mode=mask_mode,
-                                        edge_lines=True, mode=mode, return_delp_coarse=False)
+                                        edge_lines=True, mode=mode, return_delp_coarse=False, seq_window=True)
         res = core.transpose_last2(outs[0])                       # [6, z, n/f, n/f+1]
     return _restore_time(res, t, ntile)
 

@@ -68,7 +68,12 @@ enum {
 enum {
     B200CS_EXACT = 0, /* no FMA contraction, IEEE division: bit-identical to the fp32 no-FMA
                          restatement of mappm.f90 (oracle/mappm_ref.c) */
-    B200CS_FAST = 1   /* FMA contraction allowed; within the 1e-6 relative tolerance */
+    B200CS_FAST = 1,  /* hoisted-geometry arithmetic with FMA and rcp.approx; within 1e-6 of the
+                         field scale (tests/test_gpu_parity.py) */
+    /* flag, OR-ed into mode: the fx window elements were NOT contiguous in the reference's array
+       (D-grid v lines arrive as gathered columns), so numpy adds them one after the other instead
+       of pairwise; only matters for bit-exactness in B200CS_EXACT */
+    B200CS_SEQ_WINDOW = 2
 };
 
 int b200cs_version(void);

@@ -20,6 +20,7 @@ struct HostAcc {
     float q(int f) const { return qv[f]; }
     float pe(float) const { return pv; }
     float pe0() const { return pe1[0]; }
+    void rewind() {}
 };
 
 template <int NF>
