@@ -8,8 +8,14 @@
 //   * every quantity that depends only on the pressure geometry is formed once per source layer
 //     and shared by the NF fields: the slope factors A,B (mappm.f90:658-662 with the divisions
 //     hoisted), the edge factors G1,G2,G3 (:674-683 expanded in d01, dc(k-1), dc(k)), 1/dp for the
-//     sub-layer coordinates, and per integration piece the three weights (dP, dP*PS, -dP*TT) so
-//     that a field costs 3 FMAs per piece (:76-112);
+//     sub-layer coordinates;
+//   * the integrals of :76-112 are taken in "mean + deviation" form.  With s the position of an
+//     output edge inside source layer L (0..1) and D(s) = dp*s*(1-s)*[(A6/3)(1+s) - B],
+//     B = (A6+AR-AL)/2, the mass of layer L above the edge is q*dp*s + D(s) (D(0) = D(1) = 0).
+//     Every output edge is evaluated ONCE (it closes one output layer and opens the next: the
+//     running sum R keeps -D for the layer it opens), whole and partial layers enter through
+//     q*dP, and no difference of large numbers is formed.  A field costs 5 flops per output
+//     layer plus one FMA per source layer, and only (q, A6/3, B) are kept per layer;
 //   * divisions by geometry become MUFU.RCP (rcp.approx, <= 1 ulp); no per-field division is left;
 //   * max3(q)-q and q-min3(q) of :664-666 are evaluated on the differences, max3(0,-d01,d12) and
 //     max3(0,d01,-d12): identical values (rounding is monotone), two subtractions fewer;
@@ -57,32 +63,29 @@ struct PpmFast {
     float q0[NF], q1[NF], q2[NF];  // q[L], q[L+1], q[L+2]
     float e1[NF];                // pre-limiter edge value at interface L+1
     float dc1[NF];               // limited slope of layer L+1
-    float al[NF], bb[NF], a6[NF];  // limited parabola of layer L: AL, (A6+AR-AL)/2, A6
+    float a63[NF], bb[NF];       // limited parabola of layer L: A6/3 and B = (A6+AR-AL)/2
+    float R[NF];                 // running mass of the output layer being filled (see remap)
     float ebot[NF];              // edge value at the surface, valid once L >= km-2
     float qtop[NF];
 
     // parabola of layer L from its edge values (l, r), mean a1 and limited slope dm;
-    // mappm.f90:773-778,844-849 with ppm_limiters lmt=0 (:875-894)
+    // mappm.f90:773-778,844-849 with ppm_limiters lmt=0 (:875-894), in deviations from the mean:
+    // dl = AL-a1, dr = AR-a1.  Unlimited: A6 = -3(dl+dr), B = -2dl-dr.  The limiter's tests
+    // A6*dA < -dA^2 / > dA^2 (dA = AR-AL; kept literally: they are discontinuous at dA = 0) pick
+    // the edge x to keep: A6 = 3x and B = 0 (x = dl) or 3x (x = dr).
+    // dm == 0 (local extremum): flat, A6 = B = 0.
     B200CS_HD void make_parabola(int f, float l, float r, float a1, float dm) {
-        // dm == 0 (local extremum): flat layer.  Folding it into the edge values makes every
-        // later quantity come out as the Fortran sets it (A6 = 0, AL = AR = a1).
+        const float dl = l - a1, dr = r - a1;
+        const float sm = dl + dr, df = r - l;
+        const float ta = (3.f * sm) * df;  // -A6*dA
+        const bool lim = fabsf(ta) > df * df;
+        const bool neg = ta > 0.f;         // A6*dA < 0: keep AL
+        const float x = neg ? dl : dr;
+        const float a = lim ? x : -sm;
+        const float b = lim ? (neg ? 0.f : 3.f * x) : (-2.f * dl - dr);
         const bool flat = (dm == 0.f);
-        l = flat ? a1 : l;
-        r = flat ? a1 : r;
-        const float a = 3.f * (2.f * a1 - (l + r));
-        const float da1 = r - l;
-        const float t = a * da1, da2 = da1 * da1;
-        // :877-890.  t < -da2: keep AL, A6 = 3(AL-a1), AR = AL-A6;  t > da2: keep AR, A6 = 3(AR-a1),
-        // AL = AR-A6.  In both, A6 = 3(e-a1) with e the kept edge and the other edge is e-A6, so
-        // (AL, A6, (A6+AR-AL)/2) = (l, x3, 0) or (e-x3, x3, x3).
-        const bool lim = fabsf(t) > da2;
-        const bool neg = t < 0.f;
-        const float e = neg ? l : r;
-        const float x3 = 3.f * (e - a1);
-        const float o = e - x3;
-        al[f] = (lim && !neg) ? o : l;
-        a6[f] = lim ? x3 : a;
-        bb[f] = lim ? (neg ? 0.f : x3) : 0.5f * (a + da1);
+        a63[f] = flat ? 0.f : a;
+        bb[f] = flat ? 0.f : b;
     }
 
     template <class Acc>
@@ -146,6 +149,7 @@ struct PpmFast {
                 q0[f] = qa; q1[f] = qb; q2[f] = qC[f];
                 qtop[f] = qa;
                 ebot[f] = 0.f;
+                R[f] = 0.f;
             }
         }
         L = 0;
@@ -255,45 +259,54 @@ struct PpmFast {
         for (int f = 0; f < NF; f++) make_parabola(f, dl[f], e1[f], q0[f], dm[f]);
     }
 
-    // One output layer [pt, pb] (rdpc = 1/(pb-pt)); mappm.f90:58-124.
+    // Positions the machine on the first output edge p (only needed when p > pe[0]; the fused
+    // kernel's output grid starts at pe[0], where R = 0 from init() is already right).
+    template <class Acc>
+    B200CS_HD void open(Acc& a, float p) {
+        while (p > pe_hi && L < km - 1) advance(a);
+        const float h = fminf(fmaxf(p, pe_lo), pe_hi) - pe_lo;
+        const float s = h * rdp0;
+        const float nc = h * (s - 1.f);
+        const float u = 1.f + s;
+        const bool inside = (p > pe_lo) && (p <= pe_hi);
+#pragma unroll
+        for (int f = 0; f < NF; f++) R[f] = inside ? nc * (a63[f] * u - bb[f]) : 0.f;
+    }
+
+    // One output layer [pt, pb] (rdpc = 1/(pb-pt)); mappm.f90:58-124.  Must be called for
+    // consecutive output layers (pt = the previous call's pb), starting at pt = pe[0] or after
+    // open(pt).
     template <class Acc>
     B200CS_HD void remap(Acc& a, float pt, float pb, float rdpc, float (&out)[NF]) {
-        if (pt <= pe_top) {  // :62-64
+        // source layers that end above pb: the part of them below pt enters through the mean
+        // (:99-104 for whole layers; for the layer holding pt, R already carries -D(pt))
+        while (pb > pe_hi && L < km - 1) {
+            if (pt < pe_hi) {  // false while the level search skips layers above pt (:70-74)
+                const float d = pe_hi - fmaxf(pt, pe_lo);
 #pragma unroll
-            for (int f = 0; f < NF; f++) out[f] = qtop[f];
-            return;
-        }
-        float qsum[NF];
-#pragma unroll
-        for (int f = 0; f < NF; f++) qsum[f] = 0.f;
-        const bool above_surface = pt < pe_surf;
-        while (true) {
-            if (above_surface && pt <= pe_hi) {  // the part of [pt,pb] inside layer L
-                const float lo = fmaxf(pt, pe_lo), hi = fminf(pb, pe_hi);
-                const float s1 = (lo - pe_lo) * rdp0, s2 = (hi - pe_lo) * rdp0;
-                const float w0 = hi - lo;
-                const float ps = s1 + s2;
-                const float w1 = w0 * ps;
-                const float w2 = w0 * ((-1.f / 3.f) * (s1 * s1 + s2 * ps));
-                // a source layer strictly inside the output layer enters through its MEAN, not its
-                // parabola (:99-104) -- the two differ when a neighbour's NaN poisons the edges
-                const bool whole = (pt < pe_lo) && (pb > pe_hi);
-#pragma unroll
-                for (int f = 0; f < NF; f++) {
-                    if (whole) qsum[f] = qsum[f] + w0 * q0[f];
-                    else qsum[f] = qsum[f] + w0 * al[f] + w1 * bb[f] + w2 * a6[f];
-                }
+                for (int f = 0; f < NF; f++) R[f] = R[f] + d * q0[f];
             }
-            if (pb <= pe_hi || L >= km - 1) break;
             advance(a);
         }
-        if (pb > pe_surf && L >= km - 1) {  // below the source column: constant extension, :65-67,115-120
-            const float ext = pb - fmaxf(pt, pe_surf);
+        // pb lies in layer L -- or below the surface (L == km-1): the mean then extends downwards
+        // (:65-67,115-120) and the edge sits at s = 1 where D vanishes
+        const float d = pb - fmaxf(pt, pe_lo);
+        const float h = fminf(pb, pe_hi) - pe_lo;
+        const float s = h * rdp0;
+        const float nc = h * (s - 1.f);  // -dp*s*(1-s)
+        const float u = 1.f + s;
+        const bool inside = pb <= pe_hi;
 #pragma unroll
-            for (int f = 0; f < NF; f++) qsum[f] = qsum[f] + ext * q0[f];
+        for (int f = 0; f < NF; f++) {
+            const float t = a63[f] * u - bb[f];
+            const float nD = inside ? nc * t : 0.f;  // -D(s)
+            out[f] = ((R[f] + d * q0[f]) - nD) * rdpc;
+            R[f] = nD;
         }
+        if (pt <= pe_top) {  // :62-64: the top output layer copies the top source layer
 #pragma unroll
-        for (int f = 0; f < NF; f++) out[f] = qsum[f] * rdpc;
+            for (int f = 0; f < NF; f++) out[f] = qtop[f];
+        }
     }
 };
 

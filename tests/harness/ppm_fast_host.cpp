@@ -34,6 +34,7 @@ void run(int ncol, int km, const float* pe1, const float* const* q1, int kn, con
         b200cs::PpmFast<NF> s;
         s.init(acc, km, iv, acc.pe1[km]);
         const float* p2 = pe2 + (size_t)i * (kn + 1);
+        s.open(acc, p2[0]);
         for (int k = 0; k < kn; k++) {
             float out[NF];
             s.remap(acc, p2[k], p2[k + 1], 1.0f / (p2[k + 1] - p2[k]), out);

@@ -53,7 +53,11 @@ def run_fast(lib, pe1, qs, pe2, iv=1):
 
 def local_scale(pe1, q, pe2):
     """max|q| over the source layers (widened by the 2-layer PPM stencil) that overlap each
-    output layer -- the scale a 1e-6 relative remap error is measured against."""
+    output layer -- the scale a 1e-6 relative remap error is measured against -- times
+    max(1, source thickness / output thickness): the fast machine takes the mass of an output
+    layer as a difference of in-layer integrals, which is as accurate as the reference's sum of
+    pieces when the output grid is about as fine as the source (the fused path: coarse delp is the
+    block mean of fine delp) and loses one ulp per factor of thickness ratio otherwise."""
     ncol, km = q.shape
     kn = pe2.shape[1] - 1
     aq = np.abs(np.nan_to_num(q.astype(np.float64)))
@@ -61,8 +65,11 @@ def local_scale(pe1, q, pe2):
     for i in range(ncol):
         lo = np.clip(np.searchsorted(pe1[i], pe2[i, :-1], side="right") - 1 - 2, 0, km - 1)
         hi = np.clip(np.searchsorted(pe1[i], pe2[i, 1:], side="left") + 2, 1, km)
+        dps = np.diff(pe1[i].astype(np.float64))
+        dpt = np.diff(pe2[i].astype(np.float64))
         for k in range(kn):
-            out[i, k] = aq[i, lo[k]:max(hi[k], lo[k] + 1)].max()
+            sl = slice(lo[k], max(hi[k], lo[k] + 1))
+            out[i, k] = aq[i, sl].max() * max(1.0, dps[sl].max() / max(dpt[k], 1e-30))
     return out
 
 
