@@ -1,0 +1,403 @@
+// pressure_coarsen_sweep.cuh -- K6-fast, second design: the fused pressure-level coarse-graining
+// kernel with the SOURCE layer as the outer loop (B200CS_FAST arithmetic, fp32 data, 8-wide
+// windows, kord <= 3).  Replaces regrid_to_area_weighted_pressure -> regrid_vertical/mappm ->
+// _mask_weights -> weighted_block_average (external/vcm/vcm/cubedsphere/regridz.py:31-220,
+// external/mappm/mappm/mappm.f90, external/vcm/vcm/cubedsphere/coarsen_restarts.py:485-534).
+//
+// One CTA = 8 rows x 32 columns of fine columns, one thread per column (as pressure_coarsen.cuh).
+//   Phase A  streams delp once: block average of delp in numpy order (bit-exact) -> coarse
+//            interface pressures, 1/thickness and mask threshold per (cell, level) in shared memory.
+//   Phase B  every thread sweeps its column from the model top, ONE source layer per iteration
+//            for all threads (PpmSweep, ppm_sweep.cuh): level data arrives through a 4-deep
+//            cp.async ring in shared memory with compile-time slots; the output edges that fall
+//            into the current layer are evaluated in an inner loop and the masked, weighted
+//            values are summed over the 8 lanes of a window row (transposing butterfly when the
+//            row's lanes sit on the same output level -- the common case -- else shared-memory
+//            reductions per lane) into per-row accumulators [row][level][cell][NF+1].
+//   Phase C  rows are added in row order, one division per coarse value, coalesced stores.
+// No barrier between the start of Phase B and Phase C; HBM traffic = delp + NF fields + weights
+// read once (delp a second time through L2), coarse outputs written once.
+#pragma once
+#include "common.cuh"
+#include "ppm_sweep.cuh"
+#include "pressure_coarsen_fast.cuh"
+
+namespace b200cs {
+
+template <int NF>
+struct SweepCtx {
+    PpmSweep<NF> m;
+    const char* pf[NF];   // this column's field pointers at the next level to issue
+    const char* pd;       // same for delp
+    int64_t step_q, step_d;
+    unsigned ring;        // shared address of this thread's ring element (slot 0, value 0)
+    float pacc;           // pe[] of the last consumed level + 1 (fp32 cumsum, as Phase A)
+    // emission state
+    const float4* lvl;    // this thread's cell: [km] {pb, 1/(pb-pt), threshold, -}
+    float* acc;           // this thread's row accumulators + cell offset: [km][CW][NF+1]
+    int k;                // next output level of this lane
+    int kdone;            // (warp-uniform) output levels below this one are reduced
+    float4* buf;          // this thread's staging ring: [kStage] (stride kThreads)
+    float pt, pb, rdpc, thr;
+    float wv, wrow, psurf;
+    int km, lane, mask_mode;
+};
+
+template <int NF>
+__device__ __forceinline__ void sweep_issue(SweepCtx<NF>& c, int slot, bool valid) {
+    constexpr unsigned kValStride = kThreads * 4, kSlotStride = (NF + 1) * kThreads * 4;
+    if (valid) {
+        const unsigned dst = c.ring + slot * kSlotStride;
+#pragma unroll
+        for (int i = 0; i < NF; i++) { cp_async4(dst + i * kValStride, c.pf[i]); c.pf[i] += c.step_q; }
+        cp_async4(dst + NF * kValStride, c.pd);
+        c.pd += c.step_d;
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+template <int NF>
+__device__ __forceinline__ void sweep_read(const SweepCtx<NF>& c, int slot, float (&q)[NF], float& d) {
+    constexpr unsigned kValStride = kThreads * 4, kSlotStride = (NF + 1) * kThreads * 4;
+    const unsigned src = c.ring + slot * kSlotStride;
+#pragma unroll
+    for (int i = 0; i < NF; i++) asm volatile("ld.shared.f32 %0, [%1];" : "=f"(q[i]) : "r"(src + i * kValStride));
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(d) : "r"(src + NF * kValStride));
+}
+
+constexpr int kStage = 8;  // per-thread staging ring of weighted output values (levels)
+
+// Fallback when a lane runs more than kStage levels ahead of the slowest lane of its warp (steep
+// terrain inside one 32-column row): one butterfly pass per distinct level, lanes of other levels
+// contributing zeros.  Only this warp touches its row's accumulators and within a pass every sum
+// is written by one lane, so plain read-modify-write suffices (a shared-memory float atomicAdd
+// compiles to a CAS loop).
+template <int NF>
+__device__ __noinline__ void sweep_accumulate_slow(float* acc, int k, int lane, const float (&prod)[NF], bool on) {
+    const unsigned full = 0xffffffffu;
+    constexpr int kLevelStride = (kTileX / 8) * (NF + 1);
+    const int l8 = lane & 7;
+    const int slot = l8 < NF ? fast_owner<NF>(lane) : NF;
+    bool pending = on;
+    while (true) {
+        const unsigned kmin = __reduce_min_sync(full, pending ? (unsigned)k : 0xffffffffu);
+        if (kmin == 0xffffffffu) break;
+        const bool sel = pending && (unsigned)k == kmin;
+        float v[NF];
+#pragma unroll
+        for (int i = 0; i < NF; i++) v[i] = sel ? prod[i] : 0.f;
+        const float tot = reduce_fields8<NF>(v, lane);
+        if (l8 < NF) {  // the weight sum of every level is formed in sweep_reduce, for all lanes
+            float* dst = acc + kmin * kLevelStride + slot;
+            *dst = *dst + tot;
+        }
+        pending = pending && !sel;
+    }
+}
+
+// This lane's output values of level c.k: mask, weight, NaN -> 0, then into the staging ring.
+template <int NF>
+__device__ __forceinline__ void sweep_stage(SweepCtx<NF>& c, const float (&o)[NF], bool on) {
+    const bool keep = (c.mask_mode == B200CS_MASK_NONE) || (c.thr < c.psurf);
+    const float wk = (on && keep) ? c.wv : 0.f;
+    float prod[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) prod[i] = i < NF ? nan_to_zero(o[i < NF ? i : 0] * wk) : 0.f;
+    const bool fits = c.k - c.kdone < kStage;
+    if (on && fits) c.buf[(c.k & (kStage - 1)) * kThreads] = make_float4(prod[0], prod[1], prod[2], prod[3]);
+    if (__any_sync(0xffffffffu, on && !fits)) {
+        float pn[NF];
+#pragma unroll
+        for (int i = 0; i < NF; i++) pn[i] = prod[i];
+        sweep_accumulate_slow<NF>(c.acc, c.k, c.lane, pn, on && !fits);
+    }
+}
+
+// Reduces the staged levels every lane of the warp has passed: [c.kdone, min over lanes of k).
+template <int NF>
+__device__ __forceinline__ void sweep_reduce(SweepCtx<NF>& c) {
+    const unsigned full = 0xffffffffu;
+    constexpr int kLevelStride = (kTileX / 8) * (NF + 1);
+    const int kend = (int)__reduce_min_sync(full, (unsigned)c.k);
+    const int l8 = c.lane & 7;
+    const int slot = l8 < NF ? fast_owner<NF>(c.lane) : NF;
+    for (int kk = c.kdone; kk < kend; kk++) {
+        float4* slot_p = c.buf + (kk & (kStage - 1)) * kThreads;
+        const float4 pv = *slot_p;
+        // a slot that holds no pending level reads as zero: a lane that overflowed the ring at
+        // level kk went through sweep_accumulate_slow and must not be counted again
+        *slot_p = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float v[4] = {pv.x, pv.y, pv.z, pv.w};
+        float vn[NF];
+#pragma unroll
+        for (int i = 0; i < NF; i++) vn[i] = v[i];
+        const float tot = reduce_fields8<NF>(vn, c.lane);
+        const bool keep = (c.mask_mode == B200CS_MASK_NONE) || (c.lvl[kk].z < c.psurf);
+        float rd = c.wrow;
+        if (!__all_sync(full, keep)) rd = reduce_row8(keep ? nan_to_zero(c.wv) : 0.f);
+        if (l8 <= NF) {
+            float* dst = c.acc + kk * kLevelStride + slot;
+            *dst = *dst + (l8 < NF ? tot : rd);
+        }
+    }
+    c.kdone = kend > c.kdone ? kend : c.kdone;
+}
+
+// output edges inside the current source layer (all remaining ones when it is the last layer)
+template <int NF, int PH>
+__device__ __forceinline__ void sweep_emit(SweepCtx<NF>& c, bool last) {
+    const unsigned full = 0xffffffffu;
+    while (true) {
+        const bool can = (c.k < c.km) && (last || c.pb <= c.m.pe_hi);
+        if (!__any_sync(full, can)) break;
+        float o[NF];
+#pragma unroll
+        for (int i = 0; i < NF; i++) o[i] = 0.f;
+        if (can) c.m.template edge<PH>(c.pt, c.pb, c.rdpc, o);
+        // level 0 copies the top source layer (mappm.f90:62-64): staged before the sweep
+        sweep_stage<NF>(c, o, can && c.k > 0);
+        if (can) {
+            c.pt = c.pb;
+            c.k++;
+            const float4 lv = c.lvl[c.k < c.km ? c.k : c.km - 1];
+            c.pb = lv.x; c.rdpc = lv.y; c.thr = lv.z;
+        }
+    }
+    c.m.template close<PH>(c.pt);
+    sweep_reduce<NF>(c);
+}
+
+// one source layer L (PH = L%4; L >= 1)
+template <int NF, int PH>
+__device__ __forceinline__ void sweep_layer(SweepCtx<NF>& c, int L, int iv) {
+    const int km = c.km;
+    if (L <= km - 3) {
+        float qn[NF], d;
+        if (L >= 2) {
+            // consume level L+2 (slot (PH+2)&3), issue level L+5 into the slot of level L+1
+            sweep_issue<NF>(c, (PH + 1) & 3, L + 5 < km);
+            asm volatile("cp.async.wait_group 3;" ::: "memory");
+            sweep_read<NF>(c, (PH + 2) & 3, qn, d);
+            c.pacc = c.pacc + nan_to_zero(d);
+        } else {  // L == 1: q[3] and pe[4] are left over from init()
+            sweep_issue<NF>(c, (PH + 1) & 3, L + 5 < km);
+#pragma unroll
+            for (int i = 0; i < NF; i++) qn[i] = c.m.Q[3][i];
+        }
+        c.m.template step<PH>(c.pacc, qn);
+    } else if (L == km - 2) {
+        c.m.template step_bottom<PH>(iv);
+    } else {
+        c.m.template step_last<PH>();
+    }
+    sweep_emit<NF, PH>(c, L == km - 1);
+}
+
+template <int NF, int FY>
+__global__ void __launch_bounds__(kThreads, 2)
+pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_t fsy,
+                              const float* __restrict__ delp, int64_t ds0, int64_t dsl, int64_t dsy,
+                              const float* __restrict__ w, int64_t ws0, int64_t wsy,
+                              float* __restrict__ delp_coarse, int km, int64_t ny, int64_t nx, float toa,
+                              int mask_mode, int iv, int seq_i) {
+    constexpr int FX = 8;
+    const bool seq = seq_i != 0;
+    constexpr int CW = kTileX / FX;   // cells per tile row
+    constexpr int CH = kTileY / FY;   // cell rows per tile
+    constexpr int NCELL = CW * CH;
+    constexpr int NV = NF + 1;
+    const int tid = threadIdx.x, lane = tid & 31, ty = tid >> 5;
+    const int64_t xg = (int64_t)blockIdx.x * kTileX + lane, yg = (int64_t)blockIdx.y * kTileY + ty;
+    const int64_t b0 = blockIdx.z;
+    const bool active = (xg < nx) && (yg < ny);
+    // out-of-range threads shadow an in-range column with zero weight (keeps the warp converged)
+    const int64_t x = xg < nx ? xg : nx - 1, y = yg < ny ? yg : ny - 1;
+    const int64_t cxN = nx / FX, cyN = ny / FY;
+    // shadow threads also take the cell of the column they shadow (its levels are defined)
+    const int my_cell = (ty / FY) * CW + (int)(x - (int64_t)blockIdx.x * kTileX) / FX;
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float4* s_lvl = reinterpret_cast<float4*>(smem_raw);                    // [NCELL][km]
+    float* s_acc = reinterpret_cast<float*>(s_lvl + (size_t)NCELL * km);    // [8][km][CW][NV]
+    float* s_ring = s_acc + (size_t)kTileY * km * CW * NV;                  // [4][NV][256]
+    float* s_rows = s_ring + 4 * NV * kThreads;                             // [2][KA][8][CW]
+    float* s_den = s_rows + 2 * kFastKA * kTileY * CW;                      // [NCELL]
+    float4* s_buf = reinterpret_cast<float4*>(s_den + ((NCELL + 3) & ~3));  // [kStage][256]
+
+    SweepCtx<NF> c;
+    const float* dcol = delp + b0 * ds0 + y * dsy + x;
+    {   // start the level ring before Phase A: levels 0..3
+        const int64_t fbase = b0 * fs0 + y * fsy + x;
+#pragma unroll
+        for (int i = 0; i < NF; i++) c.pf[i] = (const char*)((const float*)fp.in[i] + fbase);
+        c.pd = (const char*)dcol;
+        c.step_q = fsl * 4; c.step_d = dsl * 4;
+        c.ring = (unsigned)__cvta_generic_to_shared(s_ring + tid);
+#pragma unroll
+        for (int j = 0; j < 4; j++) sweep_issue<NF>(c, j, true);  // km >= 4
+    }
+    for (int t = tid; t < kTileY * km * CW * NV; t += kThreads) s_acc[t] = 0.f;
+#pragma unroll
+    for (int j = 0; j < kStage; j++) s_buf[j * kThreads + tid] = make_float4(0.f, 0.f, 0.f, 0.f);
+
+    // ---------------- Phase A: coarse pressure levels of the tile's cells -------------------
+    const float wv = active ? __ldg(w + b0 * ws0 + y * wsy + x) : 0.f;
+    const float wrow = reduce_row8(nan_to_zero(wv), seq, lane);  // weight sum of this window row
+    if ((lane & (FX - 1)) == 0) s_rows[ty * CW + lane / FX] = wrow;
+    __syncthreads();
+    if (tid < NCELL) {
+        const int cyi = tid / CW, cxi = tid % CW;
+        float d = 0.f;
+        for (int r = 0; r < FY; r++) d = d + s_rows[(cyi * FY + r) * CW + cxi];
+        s_den[tid] = d;
+    }
+    __syncthreads();
+    float pacc = toa;
+    for (int k0 = 0; k0 < km; k0 += kFastKA) {
+        const int buf = (k0 / kFastKA) & 1;
+        float d[kFastKA];
+#pragma unroll
+        for (int kk = 0; kk < kFastKA; kk++)
+            d[kk] = (k0 + kk < km) ? __ldg(dcol + (int64_t)(k0 + kk) * dsl) : 0.f;
+#pragma unroll
+        for (int kk = 0; kk < kFastKA; kk++) {
+            if (k0 + kk < km) {
+                pacc = pacc + nan_to_zero(d[kk]);  // xarray cumsum == nancumsum
+                const float rs = reduce_row8(nan_to_zero(d[kk] * wv), seq, lane);
+                if ((lane & (FX - 1)) == 0) s_rows[((buf * kFastKA + kk) * kTileY + ty) * CW + lane / FX] = rs;
+            }
+        }
+        __syncthreads();
+        for (int t = tid; t < kFastKA * NCELL; t += kThreads) {
+            const int kk = t / NCELL, cc = t % NCELL, k = k0 + kk;
+            if (k < km) {
+                const int cyi = cc / CW, cxi = cc % CW;
+                float num = 0.f;
+                for (int r = 0; r < FY; r++) num = num + s_rows[((buf * kFastKA + kk) * kTileY + cyi * FY + r) * CW + cxi];
+                const float dc = num / s_den[cc];
+                s_lvl[cc * km + k].w = dc;
+                const int64_t cyg = (int64_t)blockIdx.y * CH + cyi, cxg = (int64_t)blockIdx.x * CW + cxi;
+                if (delp_coarse && cyg < cyN && cxg < cxN) delp_coarse[((b0 * km + k) * cyN + cyg) * cxN + cxg] = dc;
+            }
+        }
+    }
+    __syncthreads();
+    if (tid < NCELL) {  // coarse interfaces: sequential cumsum (exact), thresholds, 1/thickness
+        float pc = toa;
+        for (int k = 0; k < km; k++) {
+            const float dc = s_lvl[tid * km + k].w;
+            const float pn = pc + nan_to_zero(dc);
+            float thr = pn;  // PHALF: bottom interface of coarse layer k
+            if (mask_mode == B200CS_MASK_PFULL) thr = dc / (log(pn) - log(pc));
+            s_lvl[tid * km + k] = make_float4(pn, 1.0f / (pn - pc), thr, dc);
+            pc = pn;
+        }
+    }
+    __syncthreads();
+
+    // ---------------- Phase B: layer-synchronous sweep ---------------------------------------
+    c.km = km; c.lane = lane; c.mask_mode = mask_mode;
+    c.wv = wv; c.wrow = wrow; c.psurf = pacc;
+    c.lvl = s_lvl + my_cell * km;
+    c.acc = s_acc + (size_t)ty * km * CW * NV + (lane / FX) * NV;  // own window row (shadow rows: unused cells)
+    {
+        float qA[NF], qB[NF], qC[NF], qD[NF], d0, d1, d2, d3, p[5];
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        sweep_read<NF>(c, 0, qA, d0);
+        sweep_read<NF>(c, 1, qB, d1);
+        sweep_read<NF>(c, 2, qC, d2);
+        sweep_read<NF>(c, 3, qD, d3);
+        p[0] = toa;
+        p[1] = p[0] + nan_to_zero(d0);
+        p[2] = p[1] + nan_to_zero(d1);
+        p[3] = p[2] + nan_to_zero(d2);
+        p[4] = p[3] + nan_to_zero(d3);
+        c.pacc = p[4];
+        c.m.init(p, qA, qB, qC, qD, iv);
+        sweep_issue<NF>(c, 0, 4 < km);
+        sweep_issue<NF>(c, 1, 5 < km);
+        // output level 0 copies the top source layer (mappm.f90:62-64)
+        const float4 lv = c.lvl[0];
+        c.k = 0; c.pt = toa; c.pb = lv.x; c.rdpc = lv.y; c.thr = lv.z;
+        c.kdone = 0;
+        c.buf = s_buf + tid;
+        sweep_stage<NF>(c, qA, true);
+    }
+    sweep_emit<NF, 0>(c, false);  // layer 0 (km >= 4: never the last)
+    int L = 1;
+    for (; L + 3 < km; L += 4) {
+        sweep_layer<NF, 1>(c, L, iv);
+        sweep_layer<NF, 2>(c, L + 1, iv);
+        sweep_layer<NF, 3>(c, L + 2, iv);
+        sweep_layer<NF, 0>(c, L + 3, iv);
+    }
+    if (L < km) sweep_layer<NF, 1>(c, L, iv);
+    if (L + 1 < km) sweep_layer<NF, 2>(c, L + 1, iv);
+    if (L + 2 < km) sweep_layer<NF, 3>(c, L + 2, iv);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+
+    // ---------------- Phase C: rows in row order, divide, store ------------------------------
+    for (int t = tid; t < km * NCELL; t += kThreads) {
+        const int cc = t % NCELL, k = t / NCELL;
+        const int cyi = cc / CW, cxi = cc % CW;
+        const int64_t cyg = (int64_t)blockIdx.y * CH + cyi, cxg = (int64_t)blockIdx.x * CW + cxi;
+        if (cyg < cyN && cxg < cxN) {
+            float num[NF], den = 0.f;
+#pragma unroll
+            for (int i = 0; i < NF; i++) num[i] = 0.f;
+#pragma unroll
+            for (int r = 0; r < FY; r++) {
+                const float* src = s_acc + ((size_t)((cyi * FY + r) * km + k) * CW + cxi) * NV;
+#pragma unroll
+                for (int i = 0; i < NF; i++) num[i] = num[i] + src[i];
+                den = den + src[NF];
+            }
+            const int64_t o = ((b0 * km + k) * cyN + cyg) * cxN + cxg;
+#pragma unroll
+            for (int i = 0; i < NF; i++) ((float*)fp.out[i])[o] = num[i] / den;
+        }
+    }
+}
+
+template <int NF, int FY>
+size_t pressure_coarsen_sweep_smem(int km) {
+    constexpr int CW = kTileX / 8, NCELL = CW * (kTileY / FY), NV = NF + 1;
+    return (size_t)NCELL * km * sizeof(float4) +
+           sizeof(float) * ((size_t)kTileY * km * CW * NV + 4 * NV * kThreads + 2 * kFastKA * kTileY * CW + ((NCELL + 3) & ~3)) +
+           sizeof(float4) * kStage * kThreads;
+}
+
+template <int NF, int FY>
+int launch_pc_sweep(const PcArgs& a, int first) {
+    auto kern = pressure_coarsen_sweep_kernel<NF, FY>;
+    const size_t smem = pressure_coarsen_sweep_smem<NF, FY>(a.km);
+    if (smem > 227 * 1024)
+        return set_err(B200CS_EUNSUPPORTED, "pressure_coarsen(fast): km=%d needs %zu B of shared memory (> 227 KB)", a.km, smem);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return set_err(B200CS_ECUDA, "pressure_coarsen(fast): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    FieldPtrs<NF> fp;
+    for (int i = 0; i < NF; i++) { fp.in[i] = a.fields[first + i]; fp.out[i] = a.out[first + i]; }
+    dim3 grid((unsigned)((a.nx + kTileX - 1) / kTileX), (unsigned)((a.ny + kTileY - 1) / kTileY), (unsigned)a.nb0);
+    kern<<<grid, kThreads, smem, a.st>>>(fp, a.fstride[0], a.fstride[1], a.fstride[2], (const float*)a.delp,
+                                         a.dstride[0], a.dstride[1], a.dstride[2], (const float*)a.w, a.wstride[0],
+                                         a.wstride[1], first == 0 ? (float*)a.delp_coarse : nullptr, a.km, a.ny, a.nx,
+                                         (float)a.toa, a.mask_mode, a.iv, a.seq);
+    return check_launch("pressure_coarsen(fast)");
+}
+
+template <int FY>
+int launch_pc_sweep_fields(const PcArgs& a) {
+    int first = 0;
+    while (first < a.nfields) {
+        const int left = a.nfields - first;
+        int rc;
+        if (left >= 4) { rc = launch_pc_sweep<4, FY>(a, first); first += 4; }
+        else if (left >= 2) { rc = launch_pc_sweep<2, FY>(a, first); first += 2; }
+        else { rc = launch_pc_sweep<1, FY>(a, first); first += 1; }
+        if (rc != B200CS_OK) return rc;
+    }
+    return B200CS_OK;
+}
+
+}  // namespace b200cs

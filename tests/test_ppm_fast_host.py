@@ -23,16 +23,20 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 RTOL = {"walk": 1e-6, "hybrid": 1e-6, "sigma": 3e-6, "wild": 3e-6}
 
 
-@pytest.fixture(scope="module")
-def harness():
-    src = os.path.join(HERE, "harness", "ppm_fast_host.cpp")
-    so = os.path.join(HERE, "harness", "libppm_fast_host.so")
-    hdrs = [os.path.join(HERE, "..", "fv3net_b200", "csrc", h) for h in ("ppm_fast.cuh", "ppm_stream.cuh")]
+@pytest.fixture(scope="module", params=["fast", "sweep"])
+def harness(request):
+    """both FAST column machines: ppm_fast.cuh (output-layer-major) and ppm_sweep.cuh
+    (source-layer-major, the one the fast fused kernel runs)"""
+    name = request.param
+    src = os.path.join(HERE, "harness", f"ppm_{name}_host.cpp")
+    so = os.path.join(HERE, "harness", f"libppm_{name}_host.so")
+    hdrs = [os.path.join(HERE, "..", "fv3net_b200", "csrc", h) for h in ("ppm_fast.cuh", "ppm_stream.cuh", "ppm_sweep.cuh")]
     if (not os.path.exists(so)) or max(os.path.getmtime(p) for p in [src] + hdrs) > os.path.getmtime(so):
         subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-x", "c++", src, "-o", so])
     lib = ctypes.CDLL(so)
-    lib.ppm_fast_host.restype = ctypes.c_int
-    return lib
+    fn = getattr(lib, f"ppm_{name}_host")
+    fn.restype = ctypes.c_int
+    return fn
 
 
 def run_fast(lib, pe1, qs, pe2, iv=1):
@@ -46,7 +50,7 @@ def run_fast(lib, pe1, qs, pe2, iv=1):
     arr_t = fp * len(qs)
     qin = arr_t(*[q.ctypes.data_as(fp) for q in qs])
     qout = arr_t(*[o.ctypes.data_as(fp) for o in outs])
-    rc = lib.ppm_fast_host(len(qs), ncol, km, pe1.ctypes.data_as(fp), qin, kn, pe2.ctypes.data_as(fp), qout, int(iv))
+    rc = lib(len(qs), ncol, km, pe1.ctypes.data_as(fp), qin, kn, pe2.ctypes.data_as(fp), qout, int(iv))
     assert rc == 0
     return outs
 

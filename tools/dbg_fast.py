@@ -15,7 +15,10 @@ def sprinkle_nans(rng, a, frac):
     a = a.copy(); a[rng.uniform(size=a.shape) < frac] = np.nan; return a
 
 small = "--small" in sys.argv
-for (n, nfields) in ([(64, 2)] if small else [(64, 2), (64, 5), (64, 4)]):
+cases = [(64, 2)] if small else [(64, 2), (64, 5), (64, 4)]
+if "--case" in sys.argv:
+    i = sys.argv.index("--case"); cases = [(int(sys.argv[i + 1]), int(sys.argv[i + 2]))]
+for (n, nfields) in cases:
     rng = np.random.default_rng(99 + n + nfields)
     nb, km, f = (1 if small else 6), 79, 8
     delp = _synthetic_columns(rng, 6, km, n, np.float32)
