@@ -34,6 +34,8 @@ struct PpmSweep {
     float r12;              // 1/(dp[L+1]+dp[L+2]) formed by the previous step
     float rdp0;             // 1/dp[L]
     float pe_lo, pe_hi;     // pe[L], pe[L+1] of the current layer (copies: used by every edge)
+    float qc[NF];           // q[L] of the current layer (copy: the edge code is phase-independent,
+                            // one instance instead of four keeps the hot loop inside the i-cache)
 
     // ppm_limiters lmt=0 in deviation form; see PpmFast::make_parabola
     B200CS_HD void make_parabola(int f, float l, float r, float a1, float dm) {
@@ -87,6 +89,7 @@ struct PpmSweep {
             E[1][f] = x2;          // interface 1
             DC[1][f] = s2[f];      // layer 1
             R[f] = 0.f;
+            qc[f] = qa;
             make_parabola(f, x1, x2, qa, dc0);
         }
         PE[0] = p[0]; PE[1] = p[1]; PE[2] = p[2]; PE[3] = p[3];
@@ -135,6 +138,7 @@ struct PpmSweep {
             const float dm = DC[e0][f];
             const float en = q0 + G1 * d01 + G2 * dm - G3 * dcn;
             make_parabola(f, E[e0][f], en, q0, dm);
+            qc[f] = q0;
             E[e1][f] = en;
             DC[e1][f] = dcn;
         }
@@ -174,6 +178,7 @@ struct PpmSweep {
                 if (qkm * r <= 0.f) r = 0.f;
             }
             make_parabola(f, ekm2, l, qkm1, DC[e0][f]);
+            qc[f] = qkm1;
             E[e1][f] = l;
             DC[e1][f] = dckm;
             E[e0][f] = r;  // interface km has the parity of interface km-2
@@ -188,37 +193,40 @@ struct PpmSweep {
         pe_lo = PE[i0]; pe_hi = PE[i1];
         rdp0 = fast_rcp(DP[i0]);
 #pragma unroll
-        for (int f = 0; f < NF; f++) make_parabola(f, E[e0][f], E[e1][f], Q[i0][f], DC[e0][f]);
+        for (int f = 0; f < NF; f++) {
+            make_parabola(f, E[e0][f], E[e1][f], Q[i0][f], DC[e0][f]);
+            qc[f] = Q[i0][f];
+        }
     }
 
     // Output edge pb inside the current layer (pb <= pe_hi), or below the surface when the current
     // layer is the last one: closes the output layer [pt, pb] (rdpc = 1/(pb-pt)) and opens the
-    // next.  mappm.f90:76-120 in the mean + deviation form of ppm_fast.cuh.  PH = L%4.
-    template <int PH>
+    // next.  mappm.f90:76-120 in the mean + deviation form of ppm_fast.cuh.
+    // LAST = false: pb <= pe_hi is known (the caller tested it), the edge is inside the layer.
+    template <bool LAST = true>
     B200CS_HD void edge(float pt, float pb, float rdpc, float (&out)[NF]) {
         const float d = pb - fmaxf(pt, pe_lo);
-        const float h = fminf(pb, pe_hi) - pe_lo;
+        const float h = (LAST ? fminf(pb, pe_hi) : pb) - pe_lo;
         const float s = h * rdp0;
-        const float nc = h * (s - 1.f);  // -dp*s*(1-s)
         const float u = 1.f + s;
-        const bool inside = pb <= pe_hi;
+        const bool inside = !LAST || pb <= pe_hi;
+        const float nc = h * (s - 1.f);  // -dp*s*(1-s)
 #pragma unroll
         for (int f = 0; f < NF; f++) {
             const float t = a63[f] * u - bb[f];
             const float nD = inside ? nc * t : 0.f;
-            out[f] = ((R[f] + d * Q[PH][f]) - nD) * rdpc;
+            out[f] = ((R[f] + d * qc[f]) - nD) * rdpc;
             R[f] = nD;
         }
     }
 
     // Leaving the current layer: what lies below the last output edge pt enters through the mean
     // (:99-104).  Nothing is added while the level search is still above pt (:70-74).
-    template <int PH>
     B200CS_HD void close(float pt) {
         if (pt < pe_hi) {
             const float d = pe_hi - fmaxf(pt, pe_lo);
 #pragma unroll
-            for (int f = 0; f < NF; f++) R[f] = R[f] + d * Q[PH][f];
+            for (int f = 0; f < NF; f++) R[f] = R[f] + d * qc[f];
         }
     }
 

@@ -98,14 +98,21 @@ __device__ __noinline__ void sweep_accumulate_slow(float* acc, int k, int lane, 
 // This lane's output values of level c.k: mask, weight, NaN -> 0, then into the staging ring.
 template <int NF>
 __device__ __forceinline__ void sweep_stage(SweepCtx<NF>& c, const float (&o)[NF], bool on) {
-    const bool keep = (c.mask_mode == B200CS_MASK_NONE) || (c.thr < c.psurf);
+    const unsigned full = 0xffffffffu;
+    const bool keep = c.thr < c.psurf;  // MASK_NONE: thr = -inf; level 0: thr = +inf (see kernel)
     const float wk = (on && keep) ? c.wv : 0.f;
     float prod[4];
 #pragma unroll
-    for (int i = 0; i < 4; i++) prod[i] = i < NF ? nan_to_zero(o[i < NF ? i : 0] * wk) : 0.f;
+    for (int i = 0; i < 4; i++) prod[i] = i < NF ? o[i < NF ? i : 0] * wk : 0.f;
+    // NaN-skipping sums (xarray's coarsen().sum()): NaNs are rare, test the lot with one vote
+    const float chk = (prod[0] + prod[1]) + (prod[2] + prod[3]);
+    if (__any_sync(full, chk != chk)) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) prod[i] = nan_to_zero(prod[i]);
+    }
     const bool fits = c.k - c.kdone < kStage;
     if (on && fits) c.buf[(c.k & (kStage - 1)) * kThreads] = make_float4(prod[0], prod[1], prod[2], prod[3]);
-    if (__any_sync(0xffffffffu, on && !fits)) {
+    if (__any_sync(full, on && !fits)) {
         float pn[NF];
 #pragma unroll
         for (int i = 0; i < NF; i++) pn[i] = prod[i];
@@ -132,7 +139,7 @@ __device__ __forceinline__ void sweep_reduce(SweepCtx<NF>& c) {
 #pragma unroll
         for (int i = 0; i < NF; i++) vn[i] = v[i];
         const float tot = reduce_fields8<NF>(vn, c.lane);
-        const bool keep = (c.mask_mode == B200CS_MASK_NONE) || (c.lvl[kk].z < c.psurf);
+        const bool keep = c.lvl[kk].z < c.psurf;
         float rd = c.wrow;
         if (!__all_sync(full, keep)) rd = reduce_row8(keep ? nan_to_zero(c.wv) : 0.f);
         if (l8 <= NF) {
@@ -144,32 +151,32 @@ __device__ __forceinline__ void sweep_reduce(SweepCtx<NF>& c) {
 }
 
 // output edges inside the current source layer (all remaining ones when it is the last layer)
-template <int NF, int PH>
-__device__ __forceinline__ void sweep_emit(SweepCtx<NF>& c, bool last) {
+template <int NF, bool LAST>
+__device__ __forceinline__ void sweep_emit(SweepCtx<NF>& c) {
     const unsigned full = 0xffffffffu;
     while (true) {
-        const bool can = (c.k < c.km) && (last || c.pb <= c.m.pe_hi);
+        // the level table ends with a +inf sentinel: lanes that are through never qualify
+        const bool can = LAST ? (c.k < c.km) : (c.pb <= c.m.pe_hi);
         if (!__any_sync(full, can)) break;
         float o[NF];
 #pragma unroll
         for (int i = 0; i < NF; i++) o[i] = 0.f;
-        if (can) c.m.template edge<PH>(c.pt, c.pb, c.rdpc, o);
-        // level 0 copies the top source layer (mappm.f90:62-64): staged before the sweep
-        sweep_stage<NF>(c, o, can && c.k > 0);
+        if (can) c.m.template edge<LAST>(c.pt, c.pb, c.rdpc, o);
+        sweep_stage<NF>(c, o, can);
         if (can) {
             c.pt = c.pb;
             c.k++;
-            const float4 lv = c.lvl[c.k < c.km ? c.k : c.km - 1];
+            const float4 lv = c.lvl[c.k];
             c.pb = lv.x; c.rdpc = lv.y; c.thr = lv.z;
         }
     }
-    c.m.template close<PH>(c.pt);
+    if (!LAST) c.m.close(c.pt);
     sweep_reduce<NF>(c);
 }
 
-// one source layer L (PH = L%4; L >= 1)
+// enter source layer L (PH = L%4; L >= 1)
 template <int NF, int PH>
-__device__ __forceinline__ void sweep_layer(SweepCtx<NF>& c, int L, int iv) {
+__device__ __forceinline__ void sweep_enter(SweepCtx<NF>& c, int L, int iv) {
     const int km = c.km;
     if (L <= km - 3) {
         float qn[NF], d;
@@ -190,7 +197,6 @@ __device__ __forceinline__ void sweep_layer(SweepCtx<NF>& c, int L, int iv) {
     } else {
         c.m.template step_last<PH>();
     }
-    sweep_emit<NF, PH>(c, L == km - 1);
 }
 
 template <int NF, int FY>
@@ -217,8 +223,8 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
     const int my_cell = (ty / FY) * CW + (int)(x - (int64_t)blockIdx.x * kTileX) / FX;
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float4* s_lvl = reinterpret_cast<float4*>(smem_raw);                    // [NCELL][km]
-    float* s_acc = reinterpret_cast<float*>(s_lvl + (size_t)NCELL * km);    // [8][km][CW][NV]
+    float4* s_lvl = reinterpret_cast<float4*>(smem_raw);                    // [NCELL][km+1], last = sentinel
+    float* s_acc = reinterpret_cast<float*>(s_lvl + (size_t)NCELL * (km + 1));  // [8][km][CW][NV]
     float* s_ring = s_acc + (size_t)kTileY * km * CW * NV;                  // [4][NV][256]
     float* s_rows = s_ring + 4 * NV * kThreads;                             // [2][KA][8][CW]
     float* s_den = s_rows + 2 * kFastKA * kTileY * CW;                      // [NCELL]
@@ -253,12 +259,17 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
     }
     __syncthreads();
     float pacc = toa;
+    float dn[kFastKA];  // next chunk of delp, in flight while the current one is reduced
+#pragma unroll
+    for (int kk = 0; kk < kFastKA; kk++) dn[kk] = (kk < km) ? __ldg(dcol + (int64_t)kk * dsl) : 0.f;
     for (int k0 = 0; k0 < km; k0 += kFastKA) {
         const int buf = (k0 / kFastKA) & 1;
         float d[kFastKA];
 #pragma unroll
+        for (int kk = 0; kk < kFastKA; kk++) d[kk] = dn[kk];
+#pragma unroll
         for (int kk = 0; kk < kFastKA; kk++)
-            d[kk] = (k0 + kk < km) ? __ldg(dcol + (int64_t)(k0 + kk) * dsl) : 0.f;
+            dn[kk] = (k0 + kFastKA + kk < km) ? __ldg(dcol + (int64_t)(k0 + kFastKA + kk) * dsl) : 0.f;
 #pragma unroll
         for (int kk = 0; kk < kFastKA; kk++) {
             if (k0 + kk < km) {
@@ -275,7 +286,7 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
                 float num = 0.f;
                 for (int r = 0; r < FY; r++) num = num + s_rows[((buf * kFastKA + kk) * kTileY + cyi * FY + r) * CW + cxi];
                 const float dc = num / s_den[cc];
-                s_lvl[cc * km + k].w = dc;
+                s_lvl[cc * (km + 1) + k].w = dc;
                 const int64_t cyg = (int64_t)blockIdx.y * CH + cyi, cxg = (int64_t)blockIdx.x * CW + cxi;
                 if (delp_coarse && cyg < cyN && cxg < cxN) delp_coarse[((b0 * km + k) * cyN + cyg) * cxN + cxg] = dc;
             }
@@ -285,20 +296,22 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
     if (tid < NCELL) {  // coarse interfaces: sequential cumsum (exact), thresholds, 1/thickness
         float pc = toa;
         for (int k = 0; k < km; k++) {
-            const float dc = s_lvl[tid * km + k].w;
+            const float dc = s_lvl[tid * (km + 1) + k].w;
             const float pn = pc + nan_to_zero(dc);
             float thr = pn;  // PHALF: bottom interface of coarse layer k
             if (mask_mode == B200CS_MASK_PFULL) thr = dc / (log(pn) - log(pc));
-            s_lvl[tid * km + k] = make_float4(pn, 1.0f / (pn - pc), thr, dc);
+            if (mask_mode == B200CS_MASK_NONE) thr = -INFINITY;  // always below the surface pressure
+            s_lvl[tid * (km + 1) + k] = make_float4(pn, 1.0f / (pn - pc), thr, dc);
             pc = pn;
         }
+        s_lvl[tid * (km + 1) + km] = make_float4(INFINITY, 0.f, INFINITY, 0.f);
     }
     __syncthreads();
 
     // ---------------- Phase B: layer-synchronous sweep ---------------------------------------
     c.km = km; c.lane = lane; c.mask_mode = mask_mode;
     c.wv = wv; c.wrow = wrow; c.psurf = pacc;
-    c.lvl = s_lvl + my_cell * km;
+    c.lvl = s_lvl + my_cell * (km + 1);
     c.acc = s_acc + (size_t)ty * km * CW * NV + (lane / FX) * NV;  // own window row (shadow rows: unused cells)
     {
         float qA[NF], qB[NF], qC[NF], qD[NF], d0, d1, d2, d3, p[5];
@@ -316,24 +329,35 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
         c.m.init(p, qA, qB, qC, qD, iv);
         sweep_issue<NF>(c, 0, 4 < km);
         sweep_issue<NF>(c, 1, 5 < km);
-        // output level 0 copies the top source layer (mappm.f90:62-64)
+        // output level 0 copies the top source layer (mappm.f90:62-64): its weighted sums go
+        // straight into the accumulators; the edge that closes level 0 still runs (it opens level
+        // 1) but stages zeros because its threshold is +inf
         const float4 lv = c.lvl[0];
-        c.k = 0; c.pt = toa; c.pb = lv.x; c.rdpc = lv.y; c.thr = lv.z;
-        c.kdone = 0;
+        c.k = 0; c.kdone = 0; c.pt = toa; c.pb = lv.x; c.rdpc = lv.y; c.thr = INFINITY;
         c.buf = s_buf + tid;
-        sweep_stage<NF>(c, qA, true);
+        {
+            const float wk0 = (lv.z < c.psurf) ? wv : 0.f;
+            float v[NF];
+#pragma unroll
+            for (int i = 0; i < NF; i++) v[i] = nan_to_zero(qA[i] * wk0);
+            const float tot = reduce_fields8<NF>(v, lane);
+            if ((lane & 7) < NF) c.acc[fast_owner<NF>(lane)] = tot;  // accumulators start at zero
+        }
     }
-    sweep_emit<NF, 0>(c, false);  // layer 0 (km >= 4: never the last)
-    int L = 1;
-    for (; L + 3 < km; L += 4) {
-        sweep_layer<NF, 1>(c, L, iv);
-        sweep_layer<NF, 2>(c, L + 1, iv);
-        sweep_layer<NF, 3>(c, L + 2, iv);
-        sweep_layer<NF, 0>(c, L + 3, iv);
+    sweep_emit<NF, false>(c);  // layer 0 (km >= 4: never the last)
+    // the windows rotate by renaming (four instances of the layer step, selected by a uniform
+    // branch); the edge / staging / reduction code exists once
+#pragma unroll 1
+    for (int L = 1; L < km; L++) {
+        switch (L & 3) {
+            case 1: sweep_enter<NF, 1>(c, L, iv); break;
+            case 2: sweep_enter<NF, 2>(c, L, iv); break;
+            case 3: sweep_enter<NF, 3>(c, L, iv); break;
+            default: sweep_enter<NF, 0>(c, L, iv); break;
+        }
+        if (L < km - 1) sweep_emit<NF, false>(c);
     }
-    if (L < km) sweep_layer<NF, 1>(c, L, iv);
-    if (L + 1 < km) sweep_layer<NF, 2>(c, L + 1, iv);
-    if (L + 2 < km) sweep_layer<NF, 3>(c, L + 2, iv);
+    sweep_emit<NF, true>(c);
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
 
@@ -363,7 +387,7 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
 template <int NF, int FY>
 size_t pressure_coarsen_sweep_smem(int km) {
     constexpr int CW = kTileX / 8, NCELL = CW * (kTileY / FY), NV = NF + 1;
-    return (size_t)NCELL * km * sizeof(float4) +
+    return (size_t)NCELL * (km + 1) * sizeof(float4) +
            sizeof(float) * ((size_t)kTileY * km * CW * NV + 4 * NV * kThreads + 2 * kFastKA * kTileY * CW + ((NCELL + 3) & ~3)) +
            sizeof(float4) * kStage * kThreads;
 }

@@ -22,12 +22,12 @@ struct Col {
                     continue;
                 }
                 float o[NF];
-                m.template edge<PH>(pt, pe2[k + 1], 1.0f / (pe2[k + 1] - pt), o);
+                m.edge(pt, pe2[k + 1], 1.0f / (pe2[k + 1] - pt), o);
                 for (int f = 0; f < NF; f++) out[f][k] = (pt <= pe1[0]) ? qp[f][0] : o[f];  // mappm.f90:62-64
                 pt = pe2[k + 1];
                 k++;
             }
-            m.template close<PH>(pt);
+            m.close(pt);
         }
     }
     template <int PH>
