@@ -199,6 +199,11 @@ __device__ __forceinline__ void sweep_enter(SweepCtx<NF>& c, int L, int iv) {
     }
 }
 
+// per-cell stride of the level table in float4 units: km+1 entries (the last is a sentinel), padded
+// to 1 mod 8 so that the tables of the cells of a tile row start 4 banks apart (a warp reads up to
+// four of them in one LDS.128)
+__host__ __device__ inline int sweep_lvl_stride(int km) { return ((km + 1 + 6) / 8) * 8 + 1; }
+
 template <int NF, int FY>
 __global__ void __launch_bounds__(kThreads, 2)
 pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_t fsy,
@@ -224,7 +229,8 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float4* s_lvl = reinterpret_cast<float4*>(smem_raw);                    // [NCELL][km+1], last = sentinel
-    float* s_acc = reinterpret_cast<float*>(s_lvl + (size_t)NCELL * (km + 1));  // [8][km][CW][NV]
+    const int LS = sweep_lvl_stride(km);
+    float* s_acc = reinterpret_cast<float*>(s_lvl + (size_t)NCELL * LS);  // [8][km][CW][NV]
     float* s_ring = s_acc + (size_t)kTileY * km * CW * NV;                  // [4][NV][256]
     float* s_rows = s_ring + 4 * NV * kThreads;                             // [2][KA][8][CW]
     float* s_den = s_rows + 2 * kFastKA * kTileY * CW;                      // [NCELL]
@@ -286,7 +292,7 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
                 float num = 0.f;
                 for (int r = 0; r < FY; r++) num = num + s_rows[((buf * kFastKA + kk) * kTileY + cyi * FY + r) * CW + cxi];
                 const float dc = num / s_den[cc];
-                s_lvl[cc * (km + 1) + k].w = dc;
+                s_lvl[cc * LS + k].w = dc;
                 const int64_t cyg = (int64_t)blockIdx.y * CH + cyi, cxg = (int64_t)blockIdx.x * CW + cxi;
                 if (delp_coarse && cyg < cyN && cxg < cxN) delp_coarse[((b0 * km + k) * cyN + cyg) * cxN + cxg] = dc;
             }
@@ -296,22 +302,22 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
     if (tid < NCELL) {  // coarse interfaces: sequential cumsum (exact), thresholds, 1/thickness
         float pc = toa;
         for (int k = 0; k < km; k++) {
-            const float dc = s_lvl[tid * (km + 1) + k].w;
+            const float dc = s_lvl[tid * LS + k].w;
             const float pn = pc + nan_to_zero(dc);
             float thr = pn;  // PHALF: bottom interface of coarse layer k
             if (mask_mode == B200CS_MASK_PFULL) thr = dc / (log(pn) - log(pc));
             if (mask_mode == B200CS_MASK_NONE) thr = -INFINITY;  // always below the surface pressure
-            s_lvl[tid * (km + 1) + k] = make_float4(pn, 1.0f / (pn - pc), thr, dc);
+            s_lvl[tid * LS + k] = make_float4(pn, 1.0f / (pn - pc), thr, dc);
             pc = pn;
         }
-        s_lvl[tid * (km + 1) + km] = make_float4(INFINITY, 0.f, INFINITY, 0.f);
+        s_lvl[tid * LS + km] = make_float4(INFINITY, 0.f, INFINITY, 0.f);
     }
     __syncthreads();
 
     // ---------------- Phase B: layer-synchronous sweep ---------------------------------------
     c.km = km; c.lane = lane; c.mask_mode = mask_mode;
     c.wv = wv; c.wrow = wrow; c.psurf = pacc;
-    c.lvl = s_lvl + my_cell * (km + 1);
+    c.lvl = s_lvl + my_cell * LS;
     c.acc = s_acc + (size_t)ty * km * CW * NV + (lane / FX) * NV;  // own window row (shadow rows: unused cells)
     {
         float qA[NF], qB[NF], qC[NF], qD[NF], d0, d1, d2, d3, p[5];
@@ -387,7 +393,7 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
 template <int NF, int FY>
 size_t pressure_coarsen_sweep_smem(int km) {
     constexpr int CW = kTileX / 8, NCELL = CW * (kTileY / FY), NV = NF + 1;
-    return (size_t)NCELL * (km + 1) * sizeof(float4) +
+    return (size_t)NCELL * sweep_lvl_stride(km) * sizeof(float4) +
            sizeof(float) * ((size_t)kTileY * km * CW * NV + 4 * NV * kThreads + 2 * kFastKA * kTileY * CW + ((NCELL + 3) & ~3)) +
            sizeof(float4) * kStage * kThreads;
 }

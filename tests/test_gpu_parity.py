@@ -443,6 +443,32 @@ def test_pressure_coarsen_fast_smooth_fields_and_options(core, oracle):
     _fast_vs_exact(core, [T[:, :, :nl] * 0.1], delp[:, :, :nl], wl, f, edge_lines=True, return_delp_coarse=False)
 
 
+def test_pressure_coarsen_host_pipeline_and_sharding(core, oracle):
+    """numpy inputs take the tile-pipelined upload path; fv3net_b200.shard slices (tile, coarse row)
+    slabs as strided views: both must reproduce the single device-resident launch bit for bit."""
+    import torch
+
+    from fv3net_b200 import shard
+
+    rng = np.random.default_rng(8)
+    nb, km, n, f = 6, 21, 64, 8
+    delp = _synthetic_columns(rng, nb, km, n, np.float32)
+    w = rng.uniform(0.5, 1.0, size=(nb, n, n)).astype(np.float32)
+    fields = [(rng.normal(size=(nb, km, n, n)) * s).astype(np.float32) for s in (1.0, 250.0, 12.0)]
+    dev = [torch.as_tensor(x).cuda() for x in fields]
+    for mode in (core.EXACT, core.FAST):
+        ref, dref = core.pressure_coarsen(dev, torch.as_tensor(delp).cuda(), torch.as_tensor(w).cuda(), f, mode=mode)
+        got, dgot = core.pressure_coarsen(fields, delp, w, f, mode=mode)  # numpy in -> numpy out, pipelined
+        assert eq(dgot, dref.cpu().numpy())
+        for a, b in zip(got, ref):
+            assert eq(a, b.cpu().numpy())
+        sh, dsh = shard.pressure_coarsen_sharded(dev, torch.as_tensor(delp).cuda(), torch.as_tensor(w).cuda(), f,
+                                                 mode=mode)
+        assert eq(dsh.cpu().numpy(), dref.cpu().numpy())
+        for a, b in zip(sh, ref):
+            assert eq(a.cpu().numpy(), b.cpu().numpy())
+
+
 # ------------------------------------------------------------------------------------------
 # the reference's regression sets through the recipe layer
 # ------------------------------------------------------------------------------------------
