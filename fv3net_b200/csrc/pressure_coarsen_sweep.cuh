@@ -249,8 +249,6 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
         for (int j = 0; j < 4; j++) sweep_issue<NF>(c, j, true);  // km >= 4
     }
     for (int t = tid; t < kTileY * km * CW * NV; t += kThreads) s_acc[t] = 0.f;
-#pragma unroll
-    for (int j = 0; j < kStage; j++) s_buf[j * kThreads + tid] = make_float4(0.f, 0.f, 0.f, 0.f);
 
     // ---------------- Phase A: coarse pressure levels of the tile's cells -------------------
     const float wv = active ? __ldg(w + b0 * ws0 + y * wsy + x) : 0.f;
@@ -264,55 +262,83 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
         s_den[tid] = d;
     }
     __syncthreads();
+    // Products delp*w go to shared memory level by level (conflict-free: one 128-B line per row);
+    // one thread per (level, cell) then adds its window rows from two LDS.128 each, in numpy's
+    // order and entirely in registers -- no shuffles.  The staging ring of Phase B is not in use
+    // yet and lends its memory.
+    constexpr int kProdLevel = kTileY * kTileX + 4;  // +4 words: levels start 4 banks apart
+    float* s_prod = reinterpret_cast<float*>(s_buf);  // [2][KA][kProdLevel]
+    static_assert(2 * kFastKA * kProdLevel * sizeof(float) <= kStage * kThreads * sizeof(float4), "s_prod must fit in s_buf");
     float pacc = toa;
     float dn[kFastKA];  // next chunk of delp, in flight while the current one is reduced
 #pragma unroll
     for (int kk = 0; kk < kFastKA; kk++) dn[kk] = (kk < km) ? __ldg(dcol + (int64_t)kk * dsl) : 0.f;
     for (int k0 = 0; k0 < km; k0 += kFastKA) {
         const int buf = (k0 / kFastKA) & 1;
-        float d[kFastKA];
+        float d[kFastKA], pr[kFastKA];
 #pragma unroll
         for (int kk = 0; kk < kFastKA; kk++) d[kk] = dn[kk];
 #pragma unroll
         for (int kk = 0; kk < kFastKA; kk++)
             dn[kk] = (k0 + kFastKA + kk < km) ? __ldg(dcol + (int64_t)(k0 + kFastKA + kk) * dsl) : 0.f;
+        float chk = 0.f;
+#pragma unroll
+        for (int kk = 0; kk < kFastKA; kk++) { pr[kk] = d[kk] * wv; chk += pr[kk]; }
+        if (__any_sync(0xffffffffu, chk != chk)) {  // NaN in delp or weights: rare, exact handling
+#pragma unroll
+            for (int kk = 0; kk < kFastKA; kk++) { d[kk] = nan_to_zero(d[kk]); pr[kk] = nan_to_zero(pr[kk]); }
+        }
+        float* sp = s_prod + (size_t)buf * kFastKA * kProdLevel + tid;
 #pragma unroll
         for (int kk = 0; kk < kFastKA; kk++) {
-            if (k0 + kk < km) {
-                pacc = pacc + nan_to_zero(d[kk]);  // xarray cumsum == nancumsum
-                const float rs = reduce_row8(nan_to_zero(d[kk] * wv), seq, lane);
-                if ((lane & (FX - 1)) == 0) s_rows[((buf * kFastKA + kk) * kTileY + ty) * CW + lane / FX] = rs;
-            }
+            pacc = pacc + d[kk];  // xarray cumsum == nancumsum (levels beyond km add 0)
+            sp[kk * kProdLevel] = pr[kk];
         }
         __syncthreads();
-        for (int t = tid; t < kFastKA * NCELL; t += kThreads) {
+        // KA*NCELL (level, cell) sums per chunk, handed to a different warp each chunk
+        const int t = (tid - (k0 / kFastKA) * 32) & (kThreads - 1);
+        if (t < kFastKA * NCELL) {
             const int kk = t / NCELL, cc = t % NCELL, k = k0 + kk;
             if (k < km) {
                 const int cyi = cc / CW, cxi = cc % CW;
+                const float* src = s_prod + (size_t)(buf * kFastKA + kk) * kProdLevel + cxi * FX;
                 float num = 0.f;
-                for (int r = 0; r < FY; r++) num = num + s_rows[((buf * kFastKA + kk) * kTileY + cyi * FY + r) * CW + cxi];
+#pragma unroll
+                for (int r = 0; r < FY; r++) {
+                    const float4 a = *reinterpret_cast<const float4*>(src + (cyi * FY + r) * kTileX);
+                    const float4 b = *reinterpret_cast<const float4*>(src + (cyi * FY + r) * kTileX + 4);
+                    float rs;
+                    if (seq) rs = ((((((((0.f + a.x) + a.y) + a.z) + a.w) + b.x) + b.y) + b.z) + b.w);
+                    else rs = ((a.x + a.y) + (a.z + a.w)) + ((b.x + b.y) + (b.z + b.w));
+                    num = num + rs;
+                }
                 const float dc = num / s_den[cc];
                 s_lvl[cc * LS + k].w = dc;
                 const int64_t cyg = (int64_t)blockIdx.y * CH + cyi, cxg = (int64_t)blockIdx.x * CW + cxi;
                 if (delp_coarse && cyg < cyN && cxg < cxN) delp_coarse[((b0 * km + k) * cyN + cyg) * cxN + cxg] = dc;
             }
         }
+        // s_prod is double-buffered: the barrier of the next chunk orders these reads before the
+        // chunk after that overwrites this half
     }
     __syncthreads();
-    if (tid < NCELL) {  // coarse interfaces: sequential cumsum (exact), thresholds, 1/thickness
+    // coarse interfaces: the cumsum is sequential (exact) and touches nothing else; meanwhile the
+    // other warps set their column machines up (fine data only)
+    if (tid < NCELL) {
         float pc = toa;
-        for (int k = 0; k < km; k++) {
-            const float dc = s_lvl[tid * LS + k].w;
-            const float pn = pc + nan_to_zero(dc);
-            float thr = pn;  // PHALF: bottom interface of coarse layer k
-            if (mask_mode == B200CS_MASK_PFULL) thr = dc / (log(pn) - log(pc));
-            if (mask_mode == B200CS_MASK_NONE) thr = -INFINITY;  // always below the surface pressure
-            s_lvl[tid * LS + k] = make_float4(pn, 1.0f / (pn - pc), thr, dc);
-            pc = pn;
+        for (int k0 = 0; k0 < km; k0 += 8) {
+            float dc[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) dc[j] = (k0 + j < km) ? s_lvl[tid * LS + k0 + j].w : 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                if (k0 + j < km) {
+                    pc = pc + nan_to_zero(dc[j]);
+                    s_lvl[tid * LS + k0 + j].x = pc;
+                }
+            }
         }
-        s_lvl[tid * LS + km] = make_float4(INFINITY, 0.f, INFINITY, 0.f);
     }
-    __syncthreads();
 
     // ---------------- Phase B: layer-synchronous sweep ---------------------------------------
     c.km = km; c.lane = lane; c.mask_mode = mask_mode;
@@ -333,6 +359,27 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
         p[4] = p[3] + nan_to_zero(d3);
         c.pacc = p[4];
         c.m.init(p, qA, qB, qC, qD, iv);
+        __syncthreads();  // coarse interface pressures are in s_lvl[].x
+        // per (cell, level): 1/thickness and the mask threshold, in parallel; sentinel entry; the
+        // staging ring (which Phase A borrowed) starts out as zeros
+        for (int t = tid; t < NCELL * (km + 1); t += kThreads) {
+            const int cc = t / (km + 1), k = t % (km + 1);
+            if (k == km) {
+                s_lvl[cc * LS + km] = make_float4(INFINITY, 0.f, INFINITY, 0.f);
+            } else {
+                const float4 e = s_lvl[cc * LS + k];
+                const float pn = e.x, dc = e.w;
+                const float pc = k > 0 ? s_lvl[cc * LS + k - 1].x : toa;
+                float thr = pn;  // PHALF: bottom interface of coarse layer k
+                if (mask_mode == B200CS_MASK_PFULL) thr = dc / (log(pn) - log(pc));
+                if (mask_mode == B200CS_MASK_NONE) thr = -INFINITY;  // always below the surface pressure
+                s_lvl[cc * LS + k].y = 1.0f / (pn - pc);
+                s_lvl[cc * LS + k].z = thr;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < kStage; j++) s_buf[j * kThreads + tid] = make_float4(0.f, 0.f, 0.f, 0.f);
+        __syncthreads();
         sweep_issue<NF>(c, 0, 4 < km);
         sweep_issue<NF>(c, 1, 5 < km);
         // output level 0 copies the top source layer (mappm.f90:62-64): its weighted sums go
