@@ -141,15 +141,16 @@ def edge_weighted_block_average(obj, spacing, coarsening_factor, edge="x"):
     return weighted_block_average(obj, spacing, coarsening_factor, edge=edge)
 
 
-def block_reduce(obj, coarsening_factor, method="sum", skipna=True, edge=None, pad=False, cval=np.nan):
+def block_reduce(obj, coarsening_factor, method="sum", skipna=True, edge=None, pad=False, cval=np.nan, window=None):
     """Block reduction of the last two axes by ``method`` in sum/mean/min/max/median/mode.
     Replaces horizontal_block_reduce / block_coarsen / block_edge_coarsen
     (cubedsphere/coarsen.py:520-683,795-840; _skimage.py:125-202).  ``pad`` pads trailing edges
-    with ``cval`` (skimage semantics); dtype is preserved."""
+    with ``cval`` (skimage semantics); dtype is preserved.  ``window`` = (fy, fx, ystep, xstep)
+    overrides the square / edge windows (1-D blocks when only one block dimension is present)."""
     if method not in _OPS:
         raise ValueError(f"unsupported reduction {method!r}; supported: {sorted(_OPS)}")
     f = int(coarsening_factor)
-    fy, fx, ystep, xstep = _window(f, edge)
+    fy, fx, ystep, xstep = _window(f, edge) if window is None else (int(v) for v in window)
     o, was_np = _to_dev(obj)
     o = o.contiguous()
     ny, nx = o.shape[-2:]
