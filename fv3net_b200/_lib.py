@@ -20,7 +20,8 @@ EXPORTS = [
     "b200cs_version", "b200cs_last_error", "b200cs_weighted_block_average", "b200cs_block_reduce",
     "b200cs_block_upsample", "b200cs_stagger", "b200cs_gather_columns", "b200cs_transpose_last2",
     "b200cs_pressure_at_interface", "b200cs_mappm_workspace_bytes", "b200cs_mappm",
-    "b200cs_pressure_coarsen", "b200cs_mask_weights",
+    "b200cs_pressure_coarsen", "b200cs_mask_weights", "b200cs_surface_pressure", "b200cs_blending_weights",
+    "b200cs_blend", "b200cs_hydrostatic_balance",
 ]
 
 _lib = None
@@ -61,6 +62,10 @@ def load():
     lib.b200cs_pressure_coarsen.argtypes = [i32, pvp, i32, p64, vp, i32, p64, vp, i32, p64, pvp, vp, i64, i32,
                                             i64, i64, i32, i32, dbl, i32, i32, i32, i32, vp]
     lib.b200cs_mask_weights.argtypes = [vp, i32, vp, vp, i32, vp, i64, i64, i64, i32, vp]
+    lib.b200cs_surface_pressure.argtypes = [vp, i32, p64, vp, i64, i32, i64, dbl, vp]
+    lib.b200cs_blending_weights.argtypes = [vp, vp, vp, i32, i64, i32, i64, dbl, dbl, vp]
+    lib.b200cs_blend.argtypes = [vp, vp, vp, vp, i32, i64, vp]
+    lib.b200cs_hydrostatic_balance.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i64, i32, i64, dbl, dbl, dbl, dbl, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
         if name not in ("b200cs_last_error", "b200cs_mappm_workspace_bytes"):

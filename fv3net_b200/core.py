@@ -450,3 +450,80 @@ def gather_columns(a, step):
 
 def transpose_last2(a):
     return gather_columns(a, 1)
+
+
+# ------------------------------------------------------------------------------------------
+# column-wise post-processing of the coarse state (SURVEY.md 8f N2; csrc/column_ops.cu)
+# ------------------------------------------------------------------------------------------
+GRAVITY, RDGAS, RVGAS = 9.80665, 287.05, 461.5  # calc/thermo/constants.py:2-4
+SIGMA_BLEND = 0.9                               # cubedsphere/coarsen_restarts.py:54
+
+
+def _zyx(t):
+    """[..., z, y, x] tensor -> contiguous, (nb, km, ncol)"""
+    t = t.contiguous()
+    km = t.shape[-3]
+    ncol = t.shape[-2] * t.shape[-1]
+    nb = int(np.prod(t.shape[:-3], dtype=np.int64))
+    return t, nb, km, ncol
+
+
+def surface_pressure(delp, toa_pressure=300.0):
+    """calc/thermo/vertically_dependent.py:189-208 for ``[..., z, y, x]``: nansum over z + toa."""
+    d, was_np = _to_dev(delp)
+    d, nb, km, ncol = _zyx(d)
+    out = torch.empty(tuple(d.shape[:-3]) + tuple(d.shape[-2:]), dtype=d.dtype, device=d.device)
+    rc = _lib.load().b200cs_surface_pressure(d.data_ptr(), _DT[d.dtype], _lib.i64arr((km * ncol, ncol)), out.data_ptr(),
+                                             nb, km, ncol, float(toa_pressure), _stream())
+    _lib.check(rc, "surface_pressure")
+    return _ret(out, was_np)
+
+
+def blending_weights(delp_coarse, ps_min, toa_pressure=300.0, sigma_blend=SIGMA_BLEND):
+    """compute_blending_weights (cubedsphere/coarsen_restarts.py:559-648) from the coarse delp
+    ``[..., z, cy, cx]`` and the block minimum of the fine surface pressure ``[..., cy, cx]``."""
+    d, was_np = _to_dev(delp_coarse)
+    p, _ = _to_dev(ps_min)
+    dt = _promote(d, p)
+    d, nb, km, ncol = _zyx(d.to(dt))
+    p = p.to(dt).contiguous()
+    if p.numel() != nb * ncol:
+        raise ValueError("blending_weights: ps_min must be delp_coarse without its vertical axis")
+    out = torch.empty_like(d)
+    rc = _lib.load().b200cs_blending_weights(d.data_ptr(), p.data_ptr(), out.data_ptr(), _DT[dt], nb, km, ncol,
+                                             float(toa_pressure), float(sigma_blend), _stream())
+    _lib.check(rc, "blending_weights")
+    return _ret(out, was_np)
+
+
+def blend(weights, pressure_level, model_level):
+    """cubedsphere/coarsen_restarts.py:651-667: weights * pressure_level + (1 - weights) * model_level."""
+    w, was_np = _to_dev(weights)
+    a, _ = _to_dev(pressure_level)
+    m, _ = _to_dev(model_level)
+    dt = _promote(w, a, m)
+    if not (w.shape == a.shape == m.shape):
+        raise ValueError("blend: weights, pressure_level and model_level must have one shape")
+    w, a, m = (t.to(dt).contiguous() for t in (w, a, m))
+    out = torch.empty_like(a)
+    rc = _lib.load().b200cs_blend(w.data_ptr(), a.data_ptr(), m.data_ptr(), out.data_ptr(), _DT[dt], a.numel(), _stream())
+    _lib.check(rc, "blend")
+    return _ret(out, was_np)
+
+
+def hydrostatic_balance(dz, phis, temperature, sphum, delp, toa_pressure=300.0):
+    """_impose_hydrostatic_balance (cubedsphere/coarsen_restarts.py:990-1017) on ``[..., z, y, x]``
+    arrays (phis ``[..., y, x]``) -> (hydrostatic DZ, adjusted phis)."""
+    z, was_np = _to_dev(dz)
+    ph, T, q, d = (_to_dev(a)[0] for a in (phis, temperature, sphum, delp))
+    dt = _promote(z, ph, T, q, d)
+    if not (z.shape == T.shape == q.shape == d.shape) or tuple(ph.shape) != tuple(z.shape[:-3]) + tuple(z.shape[-2:]):
+        raise ValueError("hydrostatic_balance: DZ, T, sphum, delp must share one shape; phis lacks the vertical axis")
+    z, nb, km, ncol = _zyx(z.to(dt))
+    ph, T, q, d = (t.to(dt).contiguous() for t in (ph, T, q, d))
+    dz_out, phis_out = torch.empty_like(z), torch.empty_like(ph)
+    rc = _lib.load().b200cs_hydrostatic_balance(z.data_ptr(), ph.data_ptr(), T.data_ptr(), q.data_ptr(), d.data_ptr(),
+                                                dz_out.data_ptr(), phis_out.data_ptr(), _DT[dt], nb, km, ncol,
+                                                float(toa_pressure), GRAVITY, RDGAS, RVGAS, _stream())
+    _lib.check(rc, "hydrostatic_balance")
+    return _ret(dz_out, was_np), _ret(phis_out, was_np)

@@ -209,3 +209,137 @@ def pressure_level_average(delp_fine, area, fields, coarsening_factor, toa_press
     shared by all fields.  Arrays ``[tile, z, y, x]``; returns (coarse fields, coarse delp)."""
     return core.pressure_coarsen(list(fields), delp_fine, area, coarsening_factor, toa_pressure, mask_mode="none",
                                  mode=mode)
+
+
+# ------------------------------------------------------------------------------------------
+# hydrostatic post-processing, blended method, whole-restart entry points (SURVEY.md 8f N2)
+# ------------------------------------------------------------------------------------------
+def impose_hydrostatic_balance(ds_fv_core, ds_fv_tracer, toa_pressure):
+    """coarsen_restarts.py:990-1017: DZ from (T, sphum, delp) in hydrostatic balance, phis
+    adjusted so that the model-top height is unchanged.  Returns a new fv_core mapping."""
+    (core_d, tracer_d), was_np = _upload(dict(ds_fv_core), {"sphum": ds_fv_tracer["sphum"]})
+    dz, phis = core.hydrostatic_balance(core_d["DZ"], core_d["phis"], core_d["T"], tracer_d["sphum"], core_d["delp"],
+                                        toa_pressure)
+    out = dict(core_d)
+    out["DZ"], out["phis"] = dz, phis
+    return _download(out, was_np)
+
+
+def blending_weights_agrid(delp, area, toa_pressure, coarsening_factor, delp_coarse=None):
+    """coarsen_restarts.py:580-621: 1 above 0.9 x the lowest fine surface pressure of the cell,
+    falling linearly (in pressure) to 0 at the coarse surface."""
+    f = coarsening_factor
+    (delp, area), was_np = _upload(delp, area)
+    if delp_coarse is None:
+        w = area
+        for _ in range(delp.ndim - 3):
+            w = w[:, None]
+        delp_coarse = core.weighted_block_average(delp, w, f)
+    ps_min = core.block_reduce(core.surface_pressure(delp, toa_pressure), f, "min")
+    out = core.blending_weights(delp_coarse, ps_min, toa_pressure)
+    return out.cpu().numpy() if was_np else out
+
+
+def blending_weights_dgrid(delp, length, toa_pressure, coarsening_factor, edge):
+    """coarsen_restarts.py:624-661: the same along coarse cell edges (delp staggered across the
+    cube faces, compute_edge_delp :825-853)."""
+    f = coarsening_factor
+    (delp, length), was_np = _upload(delp, length)
+    delp_edge = core.stagger(delp, "y" if edge == "x" else "x")
+    w = length
+    for _ in range(delp.ndim - 3):
+        w = w[:, None]
+    delp_edge_coarse = core.edge_weighted_block_average(delp_edge, w, f, edge=edge)
+    ps_min = core.block_reduce(core.surface_pressure(delp_edge, toa_pressure), f, "min", edge=edge)
+    out = core.blending_weights(delp_edge_coarse, ps_min, toa_pressure)
+    return out.cpu().numpy() if was_np else out
+
+
+def coarse_grain_fv_core_via_blended_method(ds, delp, area, dx, dy, toa_pressure, coarsening_factor,
+                                            coarsen_agrid_winds=False, mass_weighted=True, mode=EXACT):
+    """coarsen_restarts.py:700-779."""
+    f = coarsening_factor
+    (ds, delp, area, dx, dy), was_np = _upload(dict(ds), delp, area, dx, dy)
+    pl = coarse_grain_fv_core_on_pressure(ds, delp, area, dx, dy, toa_pressure, f, coarsen_agrid_winds, mode=mode)
+    ml = coarse_grain_fv_core(ds, delp, area, dx, dy, f, coarsen_agrid_winds, mass_weighted)
+    wa = blending_weights_agrid(delp, area, toa_pressure, f, delp_coarse=ml["delp"])
+    wu = blending_weights_dgrid(delp, dx, toa_pressure, f, "x")
+    wv = blending_weights_dgrid(delp, dy, toa_pressure, f, "y")
+    ignore = ["u", "v"] + ([] if coarsen_agrid_winds else ["ua", "va"])
+    out = {}
+    for v in ds:
+        if v in ignore:
+            continue
+        out[v] = core.blend(wa, pl[v], ml[v]) if ds[v].ndim == delp.ndim else ml[v]
+    out["u"] = core.blend(wu, pl["u"], ml["u"])
+    out["v"] = core.blend(wv, pl["v"], ml["v"])
+    return _download(out, was_np)
+
+
+def coarse_grain_fv_tracer_via_blended_method(ds, delp, area, toa_pressure, coarsening_factor, mass_weighted=True,
+                                              mode=EXACT):
+    """coarsen_restarts.py:782-822."""
+    f = coarsening_factor
+    (ds, delp, area), was_np = _upload(dict(ds), delp, area)
+    pl = coarse_grain_fv_tracer_on_pressure(ds, delp, area, toa_pressure, f, mode=mode)
+    ml = coarse_grain_fv_tracer(ds, delp, area, f, mass_weighted)
+    w = blending_weights_agrid(delp, area, toa_pressure, f)
+    return _download({v: core.blend(w, pl[v], ml[v]) for v in ds}, was_np)
+
+
+def _entry(restarts, grid_spec):
+    need = ("fv_core.res", "fv_srf_wnd.res", "fv_tracer.res")
+    missing = [c for c in need if c not in restarts]
+    if missing:
+        raise KeyError(f"restarts lacks the categories {missing}")
+    return restarts["fv_core.res"], restarts["fv_tracer.res"], restarts["fv_srf_wnd.res"], grid_spec["area"], \
+        grid_spec["dx"], grid_spec["dy"]
+
+
+def coarsen_restarts_on_sigma(coarsening_factor, grid_spec, toa_pressure, restarts, coarsen_agrid_winds=False,
+                              mass_weighted=True):
+    """coarsen_restarts.py:76-152 for the fv_core / fv_tracer / fv_srf_wnd categories
+    (``restarts``: category -> {name: array}; ``grid_spec``: {area, dx, dy}).  sfc_data is
+    coarse-grained by fv3net_b200.sfc_data when present."""
+    fc, ft, fs, area, dx, dy = _entry(restarts, grid_spec)
+    out = {"fv_core.res": coarse_grain_fv_core(fc, fc["delp"], area, dx, dy, coarsening_factor, coarsen_agrid_winds,
+                                               mass_weighted),
+           "fv_srf_wnd.res": coarse_grain_fv_srf_wnd(fs, area, coarsening_factor),
+           "fv_tracer.res": coarse_grain_fv_tracer(ft, fc["delp"], area, coarsening_factor, mass_weighted)}
+    return _with_sfc(out, restarts, area, coarsening_factor)
+
+
+def coarsen_restarts_on_pressure(coarsening_factor, grid_spec, toa_pressure, restarts, coarsen_agrid_winds=False,
+                                 extrapolate=False, mode=EXACT):
+    """coarsen_restarts.py:155-240, hydrostatic balance imposed on the result (:233-235)."""
+    fc, ft, fs, area, dx, dy = _entry(restarts, grid_spec)
+    f = coarsening_factor
+    out = {"fv_core.res": coarse_grain_fv_core_on_pressure(fc, fc["delp"], area, dx, dy, toa_pressure, f,
+                                                           coarsen_agrid_winds, extrapolate=extrapolate, mode=mode),
+           "fv_srf_wnd.res": coarse_grain_fv_srf_wnd(fs, area, f),
+           "fv_tracer.res": coarse_grain_fv_tracer_on_pressure(ft, fc["delp"], area, toa_pressure, f,
+                                                               extrapolate=extrapolate, mode=mode)}
+    out["fv_core.res"] = impose_hydrostatic_balance(out["fv_core.res"], out["fv_tracer.res"], toa_pressure)
+    return _with_sfc(out, restarts, area, f)
+
+
+def coarsen_restarts_via_blended_method(coarsening_factor, grid_spec, toa_pressure, restarts,
+                                        coarsen_agrid_winds=False, mass_weighted=True, mode=EXACT):
+    """coarsen_restarts.py:243-332."""
+    fc, ft, fs, area, dx, dy = _entry(restarts, grid_spec)
+    f = coarsening_factor
+    out = {"fv_core.res": coarse_grain_fv_core_via_blended_method(fc, fc["delp"], area, dx, dy, toa_pressure, f,
+                                                                  coarsen_agrid_winds, mass_weighted, mode=mode),
+           "fv_srf_wnd.res": coarse_grain_fv_srf_wnd(fs, area, f),
+           "fv_tracer.res": coarse_grain_fv_tracer_via_blended_method(ft, fc["delp"], area, toa_pressure, f,
+                                                                      mass_weighted, mode=mode)}
+    out["fv_core.res"] = impose_hydrostatic_balance(out["fv_core.res"], out["fv_tracer.res"], toa_pressure)
+    return _with_sfc(out, restarts, area, f)
+
+
+def _with_sfc(out, restarts, area, f):
+    if "sfc_data" in restarts:
+        from . import sfc_data
+
+        out["sfc_data"] = sfc_data.coarse_grain_sfc_data_complex(restarts["sfc_data"], area, f)
+    return out

@@ -215,6 +215,34 @@ int b200cs_mask_weights(const void* w, int w_dtype, const void* p_coarse, const 
                         int p_dtype, void* out, int64_t nb0, int64_t km, int64_t ncol,
                         int mask_mode, void* stream);
 
+/*
+ * Column-wise post-processing of the coarse state.  Arrays are contiguous
+ * [nb, km, ncol] (column index fastest) unless strides are given; one dtype per call.
+ *
+ * b200cs_surface_pressure: ps[nb, ncol] = nansum_k delp + toa (surface_pressure_from_delp,
+ *   VCM/calc/thermo/vertically_dependent.py:189-208); delp strided (batch, level).
+ * b200cs_blending_weights: compute_blending_weights with pfull = pressure_at_midpoint_log(delp_c),
+ *   ps = surface pressure of delp_c and blending pressure sigma_blend * ps_min, ps_min[nb, ncol]
+ *   being the block minimum of the fine surface pressure
+ *   (VCM/cubedsphere/coarsen_restarts.py:559-648).
+ * b200cs_blend: w * pressure_level + (1 - w) * model_level (coarsen_restarts.py:651-667).
+ * b200cs_hydrostatic_balance: _impose_hydrostatic_balance (coarsen_restarts.py:990-1017):
+ *   DZ from T, sphum, delp in hydrostatic balance (hydrostatic_dz, vertically_dependent.py:210-235)
+ *   and phis adjusted to keep the model-top height of (dz, phis)
+ *   (height_at_interface :69-98, dz_and_top_to_phis :182-186); phis [nb, ncol].
+ */
+int b200cs_surface_pressure(const void* delp, int dtype, const int64_t stride[2], void* ps,
+                            int64_t nb, int km, int64_t ncol, double toa_pressure, void* stream);
+int b200cs_blending_weights(const void* delp_coarse, const void* ps_min, void* out, int dtype,
+                            int64_t nb, int km, int64_t ncol, double toa_pressure,
+                            double sigma_blend, void* stream);
+int b200cs_blend(const void* weights, const void* pressure_level, const void* model_level,
+                 void* out, int dtype, int64_t n, void* stream);
+int b200cs_hydrostatic_balance(const void* dz, const void* phis, const void* temperature,
+                               const void* sphum, const void* delp, void* dz_out, void* phis_out,
+                               int dtype, int64_t nb, int km, int64_t ncol, double toa_pressure,
+                               double gravity, double rdgas, double rvgas, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -491,6 +491,112 @@ def coarse_grain_fv_srf_wnd(ds, area, f):
 
 
 # --------------------------------------------------------------------------------------
+# hydrostatic post-processing and the blended method
+# --------------------------------------------------------------------------------------
+GRAVITY, RDGAS, RVGAS = 9.80665, 287.05, 461.5  # calc/thermo/constants.py:2-4
+SIGMA_BLEND = 0.9                               # cubedsphere/coarsen_restarts.py:54
+
+
+def height_at_interface(dz, phis, z_axis=-3):
+    """calc/thermo/vertically_dependent.py:69-98: reversed nancumsum of [-dz..., phis/g]."""
+    bottom = np.expand_dims(phis, z_axis) / GRAVITY
+    dz_with_bottom = np.concatenate([-dz, np.broadcast_to(bottom, np.take(dz, [0], axis=z_axis).shape)], axis=z_axis)
+    rev = np.flip(dz_with_bottom, axis=z_axis)
+    return np.flip(np.nancumsum(rev, axis=z_axis), axis=z_axis)
+
+
+def hydrostatic_dz(T, q, delp, toa_pressure, z_axis=-3):
+    """:210-235."""
+    pi = pressure_at_interface(delp, toa_pressure, z_axis)
+    tv = T * (1 + (RVGAS / RDGAS - 1) * q)
+    with np.errstate(all="ignore"):
+        dlogp = np.diff(np.log(pi), axis=z_axis)
+    return -dlogp * RDGAS * tv / GRAVITY
+
+
+def dz_and_top_to_phis(top_height, dz, z_axis=-3):
+    """:182-186."""
+    return GRAVITY * (top_height + np.nansum(dz, axis=z_axis))
+
+
+def impose_hydrostatic_balance(core, tracer, toa_pressure, z_axis=-3):
+    """cubedsphere/coarsen_restarts.py:990-1017 -> core with DZ, phis replaced."""
+    height = height_at_interface(core["DZ"], core["phis"], z_axis)
+    height_top = np.take(height, 0, axis=z_axis)
+    dz = hydrostatic_dz(core["T"], tracer["sphum"], core["delp"], toa_pressure, z_axis)
+    out = dict(core)
+    out["DZ"] = dz
+    out["phis"] = dz_and_top_to_phis(height_top, dz, z_axis)
+    return out
+
+
+def compute_blending_weights(blending_pressure, ps_coarse, pfull_coarse):
+    """coarsen_restarts.py:559-577 (z axis at -3)."""
+    ps = np.expand_dims(ps_coarse, -3)
+    pb = np.expand_dims(blending_pressure, -3)
+    with np.errstate(all="ignore"):
+        w = (ps - pfull_coarse) / (ps - pb)
+    return np.where(pfull_coarse > pb, w, 1.0)
+
+
+def blending_weights_agrid(delp, area, toa_pressure, f):
+    """:580-621."""
+    delp_coarse = weighted_block_average(delp, _wfor(delp, area) if area.ndim == 3 else area, f)
+    pfull_coarse = pressure_at_midpoint_log(delp_coarse, toa_pressure)
+    ps = surface_pressure_from_delp(delp, toa_pressure)
+    ps_coarse = surface_pressure_from_delp(delp_coarse, toa_pressure)
+    pb = SIGMA_BLEND * coarsen_reduce(ps, f, f, "min")
+    return compute_blending_weights(pb, ps_coarse, pfull_coarse)
+
+
+def blending_weights_dgrid(delp, length, toa_pressure, f, edge):
+    """:624-661."""
+    delp_edge = stagger_delp(delp, "y" if edge == "x" else "x")
+    delp_edge_coarse = edge_weighted_block_average(delp_edge, _wfor(delp_edge, length), f, edge=edge)
+    pfull_coarse = pressure_at_midpoint_log(delp_edge_coarse, toa_pressure)
+    ps = surface_pressure_from_delp(delp_edge, toa_pressure)
+    ps_coarse = surface_pressure_from_delp(delp_edge_coarse, toa_pressure)
+    pb = SIGMA_BLEND * block_edge_coarsen(ps, f, edge=edge, method="min")
+    return compute_blending_weights(pb, ps_coarse, pfull_coarse)
+
+
+def blend(weights, pressure_level, model_level):
+    """:664-680."""
+    return weights * pressure_level + (1 - weights) * model_level
+
+
+def coarse_grain_fv_core_via_blended_method(ds, delp, area, dx, dy, toa_pressure, f, coarsen_agrid_winds=False,
+                                            mass_weighted=True, nthreads=1):
+    """:700-779."""
+    pl = coarse_grain_fv_core_on_pressure(ds, delp, area, dx, dy, toa_pressure, f, coarsen_agrid_winds,
+                                          nthreads=nthreads)
+    ml = coarse_grain_fv_core(ds, delp, area, dx, dy, f, coarsen_agrid_winds, mass_weighted)
+    wa = blending_weights_agrid(delp, area, toa_pressure, f)
+    wu = blending_weights_dgrid(delp, dx, toa_pressure, f, "x")
+    wv = blending_weights_dgrid(delp, dy, toa_pressure, f, "y")
+    out = {}
+    ignore = ["u", "v"] + ([] if coarsen_agrid_winds else ["ua", "va"])
+    for v in ds:
+        if v in ignore:
+            continue
+        if ds[v].ndim == delp.ndim:
+            out[v] = blend(wa, pl[v], ml[v])
+        else:
+            out[v] = ml[v]
+    out["u"] = blend(wu, pl["u"], ml["u"])
+    out["v"] = blend(wv, pl["v"], ml["v"])
+    return out
+
+
+def coarse_grain_fv_tracer_via_blended_method(ds, delp, area, toa_pressure, f, mass_weighted=True, nthreads=1):
+    """:782-822."""
+    pl = coarse_grain_fv_tracer_on_pressure(ds, delp, area, toa_pressure, f, nthreads=nthreads)
+    ml = coarse_grain_fv_tracer(ds, delp, area, f, mass_weighted)
+    w = blending_weights_agrid(delp, area, toa_pressure, f)
+    return {v: blend(w, pl[v], ml[v]) for v in ds}
+
+
+# --------------------------------------------------------------------------------------
 # fine_res_budget variant (workflows/fine_res_budget/budget/budgets.py:49-77)
 # --------------------------------------------------------------------------------------
 def pressure_level_average(delp_fine, delp_coarse, area, field, f, nthreads=1):

@@ -545,6 +545,86 @@ def test_dgrid_pressure_c48(restarts, oracle):
 
 
 # ------------------------------------------------------------------------------------------
+# N2: hydrostatic balance, blended method, whole-restart entry points
+# (coarsen_restarts.py:76-332, 559-779, 990-1017)
+# ------------------------------------------------------------------------------------------
+def _close(a, b, rtol, name=""):
+    assert a.shape == b.shape and np.array_equal(np.isnan(a), np.isnan(b)), name
+    np.testing.assert_allclose(a, b, rtol=rtol, atol=0, err_msg=name)
+
+
+def test_column_ops_vs_oracle(core, oracle):
+    rng = np.random.default_rng(31)
+    for dt in (np.float64, np.float32):
+        nb, km, n, f = 3, 11, 16, 4
+        delp = _synthetic_columns(rng, nb, km, n, dt)
+        area = rng.uniform(0.5, 1, size=(nb, n, n)).astype(np.float32)
+        delp[0, 2, 3, 3] = np.nan
+        ps = core.surface_pressure(delp, 300.0)
+        assert eq(ps, oracle.surface_pressure_from_delp(delp, 300.0).astype(dt))  # sequential sum: bit-exact
+        dco = oracle.weighted_block_average(delp, area[:, None], f)
+        ps_min = oracle.coarsen_reduce(oracle.surface_pressure_from_delp(delp, 300.0), f, f, "min").astype(dco.dtype)
+        w = core.blending_weights(dco, ps_min, 300.0)
+        exp = oracle.compute_blending_weights(oracle.SIGMA_BLEND * ps_min, oracle.surface_pressure_from_delp(dco, 300.0),
+                                              oracle.pressure_at_midpoint_log(dco, 300.0))
+        # log() differs by an ulp between libm and CUDA; in fp32 the difference of logs amplifies it
+        tol = 1e-11 if dco.dtype == np.float64 else 1e-3
+        _close(w, exp.astype(w.dtype), tol, "blending weights")
+        assert (w[np.isfinite(w)] <= 1.0).all() and np.all(w[:, 0] == 1.0)
+        a, m = rng.normal(size=w.shape).astype(w.dtype), rng.normal(size=w.shape).astype(w.dtype)
+        assert eq(core.blend(w, a, m), (w * a + (1 - w) * m).astype(w.dtype))
+        T = rng.uniform(200, 300, size=delp.shape).astype(dt)
+        q = rng.uniform(0, 0.02, size=delp.shape).astype(dt)
+        dz = -rng.uniform(50, 500, size=delp.shape).astype(dt)
+        phis = rng.uniform(0, 5e4, size=(nb, n, n)).astype(dt)
+        gdz, gphis = core.hydrostatic_balance(dz, phis, T, q, delp, 300.0)
+        ref = oracle.impose_hydrostatic_balance({"DZ": dz, "phis": phis, "T": T, "delp": delp}, {"sphum": q}, 300.0)
+        tol = 1e-11 if dt == np.float64 else 1e-3
+        _close(gdz, ref["DZ"].astype(dt), tol, "DZ")
+        _close(gphis, ref["phis"].astype(dt), 1e-10 if dt == np.float64 else 5e-2, "phis")
+
+
+@pytest.mark.parametrize("tag,agrid,extrapolate", [
+    ("pressure-level-with-agrid-winds", True, False),
+    ("pressure-level-without-agrid-winds", False, False),
+    ("pressure-level-extrapolate-with-agrid-winds", False, True),
+])
+def test_golden_coarsen_restarts_on_pressure(restarts, oracle, golden, tag, agrid, extrapolate):
+    core_, tracer, srf, grid = oracle.regression_inputs()
+    out = restarts.coarsen_restarts_on_pressure(2, grid, 300.0, {"fv_core.res": core_, "fv_tracer.res": tracer,
+                                                                "fv_srf_wnd.res": srf}, agrid, extrapolate)
+    for cat in ("fv_core.res", "fv_tracer.res", "fv_srf_wnd.res"):
+        _check_golden(golden, tag, cat, out[cat], 5e-6)  # the reference's own tolerance is rtol 1e-5
+
+
+@pytest.mark.parametrize("tag,agrid,mass", [("blended-area-weighted-without-agrid-winds", False, False),
+                                            ("blended-mass-weighted-with-agrid-winds", True, True)])
+def test_golden_blended(restarts, oracle, golden, tag, agrid, mass):
+    core_, tracer, srf, grid = oracle.regression_inputs()
+    out = restarts.coarsen_restarts_via_blended_method(2, grid, 300.0, {"fv_core.res": core_, "fv_tracer.res": tracer,
+                                                                       "fv_srf_wnd.res": srf}, agrid, mass)
+    for cat in ("fv_core.res", "fv_tracer.res", "fv_srf_wnd.res"):
+        _check_golden(golden, tag, cat, out[cat], 5e-6)
+    # against the oracle on the same inputs: everything but log() is the same arithmetic
+    c = oracle.coarse_grain_fv_core_via_blended_method(core_, core_["delp"], grid["area"], grid["dx"], grid["dy"],
+                                                       300.0, 2, agrid, mass)
+    t = oracle.coarse_grain_fv_tracer_via_blended_method(tracer, core_["delp"], grid["area"], 300.0, 2, mass)
+    c = oracle.impose_hydrostatic_balance(c, t, 300.0)
+    for k in c:
+        _close(out["fv_core.res"][k], c[k], 1e-9, k)
+    for k in t:
+        _close(out["fv_tracer.res"][k], t[k], 1e-9, k)
+
+
+def test_golden_coarsen_restarts_on_sigma(restarts, oracle, golden):
+    core_, tracer, srf, grid = oracle.regression_inputs()
+    out = restarts.coarsen_restarts_on_sigma(2, grid, 300.0, {"fv_core.res": core_, "fv_tracer.res": tracer,
+                                                             "fv_srf_wnd.res": srf}, True, True)
+    for cat in ("fv_core.res", "fv_tracer.res", "fv_srf_wnd.res"):
+        _check_golden(golden, "mass-weighted-model-level-with-agrid-winds", cat, out[cat], 0)
+
+
+# ------------------------------------------------------------------------------------------
 # full-size (C384, 79 levels) properties -- BASELINE configs[1..3]
 # ------------------------------------------------------------------------------------------
 def test_c384_properties(core, oracle):

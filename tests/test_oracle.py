@@ -184,3 +184,29 @@ def test_pressure_level_golden(oracle, golden, tag, agrid, extrapolate):
     _check(golden, tag, "fv_core.res", res, rtol, skip=HYDROSTATIC)
     res = oracle.coarse_grain_fv_tracer_on_pressure(tracer, core["delp"], grid["area"], 300.0, 2, extrapolate)
     _check(golden, tag, "fv_tracer.res", res, rtol)
+
+
+# ---- N2: hydrostatic balance and the blended method (coarsen_restarts.py:559-779,990-1017) ----
+@pytest.mark.parametrize("tag,agrid,extrapolate", PRESSURE_TAGS)
+def test_hydrostatic_balance_golden(oracle, golden, tag, agrid, extrapolate):
+    core, tracer, srf, grid = oracle.regression_inputs()
+    c = oracle.coarse_grain_fv_core_on_pressure(core, core["delp"], grid["area"], grid["dx"], grid["dy"],
+                                                300.0, 2, agrid, extrapolate)
+    t = oracle.coarse_grain_fv_tracer_on_pressure(tracer, core["delp"], grid["area"], 300.0, 2, extrapolate)
+    res = oracle.impose_hydrostatic_balance(c, t, 300.0)
+    _check(golden, tag, "fv_core.res", {k: res[k] for k in HYDROSTATIC}, 5e-6)
+
+
+BLENDED_TAGS = [("blended-area-weighted-without-agrid-winds", False, False),
+                ("blended-mass-weighted-with-agrid-winds", True, True)]
+
+
+@pytest.mark.parametrize("tag,agrid,mass", BLENDED_TAGS)
+def test_blended_golden(oracle, golden, tag, agrid, mass):
+    core, tracer, srf, grid = oracle.regression_inputs()
+    c = oracle.coarse_grain_fv_core_via_blended_method(core, core["delp"], grid["area"], grid["dx"], grid["dy"],
+                                                       300.0, 2, agrid, mass)
+    t = oracle.coarse_grain_fv_tracer_via_blended_method(tracer, core["delp"], grid["area"], 300.0, 2, mass)
+    c = oracle.impose_hydrostatic_balance(c, t, 300.0)
+    _check(golden, tag, "fv_core.res", c, 5e-6)
+    _check(golden, tag, "fv_tracer.res", t, 5e-6)
