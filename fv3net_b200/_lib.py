@@ -13,6 +13,8 @@ F32, F64 = 0, 1
 OP_SUM, OP_MEAN, OP_MIN, OP_MAX, OP_MEDIAN, OP_MODE = range(6)
 MASK_NONE, MASK_PHALF, MASK_PFULL = 0, 1, 2
 EXACT, FAST = 0, 1
+EW_MUL, EW_WHERE, EW_WHERE_NOT, EW_SELECT, EW_FILLNA, EW_MIN_SCALAR = range(6)
+CMP_ISCLOSE, CMP_LT, CMP_GT = range(3)
 SEQ_WINDOW = 2
 MAX_FIELDS = 16
 
@@ -21,7 +23,8 @@ EXPORTS = [
     "b200cs_block_upsample", "b200cs_stagger", "b200cs_gather_columns", "b200cs_transpose_last2",
     "b200cs_pressure_at_interface", "b200cs_mappm_workspace_bytes", "b200cs_mappm",
     "b200cs_pressure_coarsen", "b200cs_mask_weights", "b200cs_surface_pressure", "b200cs_blending_weights",
-    "b200cs_blend", "b200cs_hydrostatic_balance",
+    "b200cs_blend", "b200cs_hydrostatic_balance", "b200cs_elementwise", "b200cs_compare_scalar",
+    "b200cs_dominant_mask",
 ]
 
 _lib = None
@@ -65,6 +68,9 @@ def load():
     lib.b200cs_surface_pressure.argtypes = [vp, i32, p64, vp, i64, i32, i64, dbl, vp]
     lib.b200cs_blending_weights.argtypes = [vp, vp, vp, i32, i64, i32, i64, dbl, dbl, vp]
     lib.b200cs_blend.argtypes = [vp, vp, vp, vp, i32, i64, vp]
+    lib.b200cs_elementwise.argtypes = [i32, vp, vp, vp, vp, i32, i64, dbl, vp]
+    lib.b200cs_compare_scalar.argtypes = [i32, vp, i32, dbl, dbl, dbl, vp, vp, i64, vp]
+    lib.b200cs_dominant_mask.argtypes = [vp, vp, i32, i64, i64, i64, i32, dbl, dbl, vp, vp, vp]
     lib.b200cs_hydrostatic_balance.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i64, i32, i64, dbl, dbl, dbl, dbl, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)

@@ -25,6 +25,7 @@ UNITS = [("status", "status.cu", ["-fmad=false"]),
          ("stagger", "stagger.cu", ["-fmad=false"]),
          ("mappm", "mappm.cu", ["-fmad=false"]),
          ("column_ops", "column_ops.cu", ["-fmad=false"]),
+         ("elementwise", "elementwise.cu", ["-fmad=false"]),
          ("pc_api", "pressure_coarsen_api.cu", ["-fmad=false"]),
          ("pc_fast", "pressure_coarsen_fast.cu", ["-fmad=true"])]
 for fx in (2, 4, 8):

@@ -243,6 +243,37 @@ int b200cs_hydrostatic_balance(const void* dz, const void* phis, const void* tem
                                int dtype, int64_t nb, int km, int64_t ncol, double toa_pressure,
                                double gravity, double rdgas, double rvgas, void* stream);
 
+/*
+ * Masks and selections of the 'complex' sfc_data method (SURVEY.md 8f N1;
+ * VCM/cubedsphere/coarsen_restarts.py:1162-1470).  Masks are one byte per element (0/1).
+ *   b200cs_elementwise   MUL a*b | WHERE mask?a:scalar (`.where(mask)` with scalar = NaN) |
+ *                        WHERE_NOT mask?scalar:a (`xr.where(mask, scalar, a)`) | SELECT mask?a:b
+ *                        (`xr.where`) | FILLNA | MIN_SCALAR a<scalar?a:scalar
+ *                        (`a.where(a < scalar, other=scalar)`)
+ *   b200cs_compare_scalar  numpy.isclose(a, scalar) (VCM/xarray_utils.py:7-35) / a < scalar /
+ *                        a > scalar, optionally AND-ed with a mask
+ *   b200cs_dominant_mask isclose(fine, block_upsample_like(coarse)) without the upsampled
+ *                        temporary (coarsen_restarts.py:1173-1190), optionally AND-ed with a mask;
+ *                        fine [nb, ny, nx], coarse [nb, ny/f, nx/f]
+ */
+enum {
+    B200CS_EW_MUL = 0,
+    B200CS_EW_WHERE = 1,
+    B200CS_EW_WHERE_NOT = 2,
+    B200CS_EW_SELECT = 3,
+    B200CS_EW_FILLNA = 4,
+    B200CS_EW_MIN_SCALAR = 5
+};
+enum { B200CS_CMP_ISCLOSE = 0, B200CS_CMP_LT = 1, B200CS_CMP_GT = 2 };
+int b200cs_elementwise(int op, const void* a, const void* b, const uint8_t* mask, void* out,
+                       int dtype, int64_t n, double scalar, void* stream);
+int b200cs_compare_scalar(int cmp, const void* a, int dtype, double scalar, double rtol,
+                          double atol, const uint8_t* and_mask, uint8_t* out, int64_t n,
+                          void* stream);
+int b200cs_dominant_mask(const void* fine, const void* coarse, int dtype, int64_t nb, int64_t ny,
+                         int64_t nx, int factor, double rtol, double atol,
+                         const uint8_t* and_mask, uint8_t* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

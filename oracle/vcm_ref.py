@@ -597,6 +597,110 @@ def coarse_grain_fv_tracer_via_blended_method(ds, delp, area, toa_pressure, f, m
 
 
 # --------------------------------------------------------------------------------------
+# sfc_data, 'complex' method (cubedsphere/coarsen_restarts.py:1111-1470)
+# ds: name -> [tile, Time, y, x] (or [tile, Time, z, y, x] for stc/smc/slc); area [tile, y, x]
+# --------------------------------------------------------------------------------------
+FREEZING_TEMPERATURE, SHDMIN_THRESHOLD, STYPE_LAND_ICE, VTYPE_LAND_ICE = 273.16, 0.011, 16.0, 15.0  # :48-51
+
+
+def _block_mode_omit(a, f):
+    red = lambda arr, axis: mode_reduce(arr, axis, nan_policy="omit")  # noqa: E731
+    return horizontal_block_reduce(a, f, red)
+
+
+def _where(a, mask):
+    return np.where(mask, a, np.nan)
+
+
+def _wb(a, w, f):
+    """weighted_block_average with weights [tile, (Time,) y, x] broadcast over a's extra z axis."""
+    if a.ndim == w.ndim + 1:
+        w = np.expand_dims(w, -3)
+    with np.errstate(all="ignore"):
+        return weighted_block_average(a, w, f)
+
+
+def sfc_precompute(ds, f):
+    """:1162-1206."""
+    slmsk_c = _block_mode_omit(ds["slmsk"], f)
+    dom_sfc = np.isclose(ds["slmsk"], block_upsample(slmsk_c, f))
+    vtype_c = _block_mode_omit(_where(ds["vtype"], dom_sfc), f)
+    stype_c = _block_mode_omit(_where(ds["stype"], dom_sfc), f)
+    dom_v = np.isclose(ds["vtype"], block_upsample(vtype_c, f))
+    dom_s = np.isclose(ds["stype"], block_upsample(stype_c, f))
+    return slmsk_c, vtype_c, stype_c, dom_sfc, dom_v, dom_s
+
+
+SFC_AREA = ["tsea", "alvsf", "alvwf", "alnsf", "alnwf", "facsf", "facwf", "f10m", "t2m", "q2m", "uustar", "ffmm",
+            "ffhh", "tprcp", "snwdph"]
+SFC_DOMINANT = ["tg3", "vfrac", "fice", "sncovr", "shdmin", "shdmax", "snoalb"]
+SFC_VTYPE = ["canopy", "zorl"]
+SFC_STYPE = ["smc", "slc", "stc"]
+
+
+def coarse_grain_sfc_data_complex(ds, area, f):
+    """:1111-1159 with the method table :1360-1393 and the chgres corrections :1396-1470."""
+    slmsk_c, vtype_c, stype_c, dom_sfc, dom_v, dom_s = sfc_precompute(ds, f)
+    a = np.broadcast_to(area[:, None], ds["slmsk"].shape).astype(area.dtype)
+    out = {"slmsk": slmsk_c, "vtype": vtype_c, "stype": stype_c}
+
+    def m3(mask, v):  # a 2-D mask against a possibly 3-D variable
+        return np.expand_dims(mask, -3) if v.ndim == mask.ndim + 1 else mask
+
+    for name, v in ds.items():
+        if name in out:
+            continue
+        if name in SFC_AREA:
+            r = _wb(v, a, f)
+        elif name in SFC_DOMINANT:
+            r = _wb(_where(v, dom_sfc), _where(a, dom_sfc), f)
+        elif name in SFC_VTYPE:
+            mask = dom_sfc & dom_v
+            aw = _wb(_where(v, mask), _where(a, mask), f)
+            avw = _wb(_where(v, mask), _where(a * ds["vfrac"], mask), f)
+            tot = coarsen_sum(_where(a * ds["vfrac"], mask), f, f)
+            r = np.where(tot > 0.0, avw, aw)
+        elif name in SFC_STYPE:
+            mask = dom_sfc & dom_s
+            r = _wb(_where(v, m3(mask, v)), _where(a, mask), f)
+        elif name == "srflag":
+            r = _block_mode_omit(v, f)
+        elif name == "slope":
+            r = _block_mode_omit(_where(v, dom_sfc), f)
+        elif name in ("sheleg", "hice"):
+            r = _wb(v, a * ds["sncovr" if name == "sheleg" else "fice"], f)
+            r = np.where(np.isnan(r), 0.0, r)
+        elif name == "tisfc":
+            sea_ice = _wb(_where(v, dom_sfc), _where(a * ds["fice"], dom_sfc), f)
+            other = _wb(_where(v, dom_sfc), _where(a, dom_sfc), f)
+            r = np.where(np.isclose(slmsk_c, 2.0), sea_ice, other)
+        else:
+            raise KeyError(f"no sfc_data coarsening method for {name!r}")
+        out[name] = r
+    # surface_chgres corrections, in order
+    land_ice = np.isclose(out["vtype"], VTYPE_LAND_ICE)
+    for k in ("tsea", "tg3"):
+        clipped = np.where(out[k] < FREEZING_TEMPERATURE, out[k], FREEZING_TEMPERATURE)
+        out[k] = np.where(land_ice, clipped, out[k])
+    out["stype"] = np.where(land_ice, STYPE_LAND_ICE, out["stype"])
+    out["canopy"] = np.where(out["shdmin"] < SHDMIN_THRESHOLD, 0.0, out["canopy"])
+    out["shdmin"] = np.where(land_ice, 0.0, out["shdmin"])
+    return {k: (v.astype(np.float32) if v.dtype == np.float64 else v) for k, v in out.items()}  # _doubles_to_floats
+
+
+def sfc_regression_inputs():
+    """The sfc_data inputs of test_coarsen_restarts.py (schemas/sfc_data-schema.json): float64,
+    [6, 1, 4, 4] (stc/smc/slc [6, 1, 4, 4, 4]), every array drawn with np.random.seed(0)."""
+    names2 = ["slmsk", "tsea", "sheleg", "tg3", "zorl", "alvsf", "alvwf", "alnsf", "alnwf", "facsf", "facwf", "vfrac",
+              "canopy", "f10m", "t2m", "q2m", "vtype", "stype", "uustar", "ffmm", "ffhh", "hice", "fice", "tisfc",
+              "tprcp", "srflag", "snwdph", "shdmin", "shdmax", "slope", "snoalb", "sncovr"]
+    ds = {n: synth_array((6, 1, 4, 4), np.float64) for n in names2}
+    for n in ("stc", "smc", "slc"):
+        ds[n] = synth_array((6, 1, 4, 4, 4), np.float64)
+    return ds
+
+
+# --------------------------------------------------------------------------------------
 # fine_res_budget variant (workflows/fine_res_budget/budget/budgets.py:49-77)
 # --------------------------------------------------------------------------------------
 def pressure_level_average(delp_fine, delp_coarse, area, field, f, nthreads=1):

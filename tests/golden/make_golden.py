@@ -3,8 +3,8 @@ compact fixture that can travel to the GPU box (where /root/reference does not e
 
 Source: /root/reference/external/vcm/tests/_coarsen_restarts_regression_tests/reference/*.json
 (7 regression tags of external/vcm/tests/test_coarsen_restarts.py:32-61; written by the
-reference itself with `to_json`).  Only the categories on the hot path are kept
-(fv_core.res, fv_tracer.res, fv_srf_wnd.res); sfc_data is a "next" row.
+reference itself with `to_json`).  All four restart categories are kept
+(fv_core.res, fv_tracer.res, fv_srf_wnd.res and sfc_data -- the "next" row N1 of SURVEY.md 8f).
 Inputs are NOT stored: they regenerate bit-exactly from np.random.seed(0) (see
 oracle/vcm_ref.regression_inputs, external/synth/synth/core.py:59-67).
 
@@ -20,7 +20,7 @@ import numpy as np
 
 REF = "/root/reference/external/vcm/tests/_coarsen_restarts_regression_tests/reference"
 OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "coarsen_restarts_golden.npz")
-CATEGORIES = ["fv_core.res", "fv_tracer.res", "fv_srf_wnd.res"]
+CATEGORIES = ["fv_core.res", "fv_tracer.res", "fv_srf_wnd.res", "sfc_data"]
 
 
 def main():

@@ -655,3 +655,58 @@ def test_c384_properties(core, oracle):
     # (6) mass-weighted == area-weighted with precomputed mass (config 1)
     mw = core.weighted_block_average(T, area[:, None], f, weights2=delp)
     assert torch.equal(mw, core.weighted_block_average(T, delp * area[:, None], f))
+
+
+# ------------------------------------------------------------------------------------------
+# N1: sfc_data, 'complex' method (coarsen_restarts.py:1111-1470)
+# ------------------------------------------------------------------------------------------
+def test_golden_sfc_data(oracle, golden, core):
+    from fv3net_b200 import sfc_data
+
+    _, _, _, grid = oracle.regression_inputs()
+    ds = oracle.sfc_regression_inputs()
+    res = sfc_data.coarse_grain_sfc_data_complex(ds, grid["area"], 2)
+    assert set(res) == set(ds)
+    for k, v in res.items():
+        assert v.dtype == np.float32, k
+    _check_golden(golden, "pressure-level-with-agrid-winds", "sfc_data", res, 0)  # bit-exact
+
+
+def _realistic_sfc(rng, n=16, nz=4):
+    """categorical surface types with real ties, fractions in [0, 1], NaNs, land ice"""
+    shape = (6, 1, n, n)
+    ds = {"slmsk": rng.integers(0, 3, size=shape).astype(np.float64),
+          "vtype": rng.choice([0.0, 7.0, 10.0, 15.0], size=shape), "stype": rng.choice([0.0, 3.0, 9.0, 16.0], size=shape),
+          "srflag": rng.integers(0, 2, size=shape).astype(np.float64), "slope": rng.integers(0, 5, size=shape).astype(np.float64)}
+    for k in ("vfrac", "fice", "sncovr", "shdmin", "shdmax", "snoalb", "canopy"):
+        ds[k] = rng.uniform(0, 1, size=shape) * (rng.random(shape) > 0.3)
+    ds["shdmin"] = ds["shdmin"] * 0.05
+    for k in ("tsea", "tg3", "tisfc", "t2m"):
+        ds[k] = rng.uniform(250, 300, size=shape)
+    for k in ("zorl", "sheleg", "hice", "alvsf", "q2m", "snwdph"):
+        ds[k] = rng.uniform(0, 10, size=shape)
+    for k in ("stc", "smc", "slc"):
+        ds[k] = rng.uniform(0, 300, size=(6, 1, nz, n, n))
+    ds["tsea"][0, 0, 1, 1] = np.nan
+    ds["vfrac"][:, :, :4, :4] = 0.0  # a block where sum(area * vfrac) == 0 -> area-weighted branch
+    return ds
+
+
+@pytest.mark.parametrize("f", [2, 4, 8])
+def test_sfc_data_realistic_vs_oracle(oracle, core, f):
+    from fv3net_b200 import sfc_data
+
+    rng = np.random.default_rng(41 + f)
+    ds = _realistic_sfc(rng)
+    area = rng.uniform(0.5, 1, size=(6, 16, 16)).astype(np.float32)
+    got = sfc_data.coarse_grain_sfc_data_complex(ds, area, f)
+    exp = oracle.coarse_grain_sfc_data_complex(ds, area, f)
+    for k in exp:
+        assert eq(got[k], exp[k]), k
+    # the chgres corrections fired somewhere
+    assert (got["stype"] == 16.0).any() and (got["shdmin"] == 0.0).any()
+    simple = sfc_data.coarse_grain_sfc_data({k: ds[k] for k in ("slmsk", "tsea", "zorl")}, area, f, version="simple")
+    assert eq(simple["zorl"], oracle.horizontal_block_reduce(ds["zorl"], f, np.median))
+    assert eq(simple["slmsk"], np.round(oracle.horizontal_block_reduce(ds["slmsk"], f, np.median)))
+    with pytest.raises(ValueError, match="only supported versions"):
+        sfc_data.coarse_grain_sfc_data(ds, area, f, version="other")

@@ -210,3 +210,13 @@ def test_blended_golden(oracle, golden, tag, agrid, mass):
     c = oracle.impose_hydrostatic_balance(c, t, 300.0)
     _check(golden, tag, "fv_core.res", c, 5e-6)
     _check(golden, tag, "fv_tracer.res", t, 5e-6)
+
+
+# ---- N1: sfc_data 'complex' method (coarsen_restarts.py:1111-1470) -----------------------------
+def test_sfc_data_golden_bit_exact(oracle, golden):
+    _, _, _, grid = oracle.regression_inputs()
+    res = oracle.coarse_grain_sfc_data_complex(oracle.sfc_regression_inputs(), grid["area"], 2)
+    assert len(res) == 35
+    for tag in ("pressure-level-with-agrid-winds", "mass-weighted-model-level-with-agrid-winds",
+                "blended-area-weighted-without-agrid-winds"):
+        _check(golden, tag, "sfc_data", res, 0)
