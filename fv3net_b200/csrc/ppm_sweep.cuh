@@ -29,6 +29,7 @@ struct PpmSweep {
     float Q[4][NF];
     float PE[4], DP[4];
     float E[2][NF], DC[2][NF];
+    float DQ[2][NF];        // slot j%2: q[j+1] - q[j] (formed once, used by the steps of layers j-1 and j)
     float a63[NF], bb[NF];  // limited parabola of the current layer: A6/3, B = (A6+AR-AL)/2
     float R[NF];            // running mass of the output layer being filled (ppm_fast.cuh)
     float r12;              // 1/(dp[L+1]+dp[L+2]) formed by the previous step
@@ -88,6 +89,7 @@ struct PpmSweep {
             Q[0][f] = qa; Q[1][f] = qb; Q[2][f] = qC[f]; Q[3][f] = qD[f];
             E[1][f] = x2;          // interface 1
             DC[1][f] = s2[f];      // layer 1
+            DQ[1][f] = qC[f] - qb;
             R[f] = 0.f;
             qc[f] = qa;
             make_parabola(f, x1, x2, qa, dc0);
@@ -130,7 +132,8 @@ struct PpmSweep {
         for (int f = 0; f < NF; f++) {
             Q[i2][f] = qn[f];
             const float q0 = Q[i0][f], q1 = Q[i1][f];
-            const float d01 = q1 - q0, d12 = qn[f] - q1;
+            const float d01 = DQ[e0][f], d12 = qn[f] - q1;
+            DQ[e1][f] = d12;
             const float df2 = A * d12 + B * d01;
             const float hi = max3f(0.f, -d01, d12);
             const float lo = max3f(0.f, d01, -d12);

@@ -95,29 +95,29 @@ __device__ __noinline__ void sweep_accumulate_slow(float* acc, int k, int lane, 
     }
 }
 
-// This lane's output values of level c.k: mask, weight, NaN -> 0, then into the staging ring.
+// This lane's weighted output values of level c.k (mask and weight already applied by the edge
+// evaluation): NaN -> 0, then into the staging ring.
 template <int NF>
 __device__ __forceinline__ void sweep_stage(SweepCtx<NF>& c, const float (&o)[NF], bool on) {
     const unsigned full = 0xffffffffu;
-    const bool keep = c.thr < c.psurf;  // MASK_NONE: thr = -inf; level 0: thr = +inf (see kernel)
-    const float wk = (on && keep) ? c.wv : 0.f;
     float prod[4];
 #pragma unroll
-    for (int i = 0; i < 4; i++) prod[i] = i < NF ? o[i < NF ? i : 0] * wk : 0.f;
-    // NaN-skipping sums (xarray's coarsen().sum()): NaNs are rare, test the lot with one vote
+    for (int i = 0; i < 4; i++) prod[i] = i < NF ? o[i < NF ? i : 0] : 0.f;
+    // NaN-skipping sums (xarray's coarsen().sum()) and ring overflow are both rare: one vote
     const float chk = (prod[0] + prod[1]) + (prod[2] + prod[3]);
-    if (__any_sync(full, chk != chk)) {
+    const bool fits = c.k - c.kdone < kStage;
+    const bool over = on && !fits;
+    if (__any_sync(full, (chk != chk) || over)) {
 #pragma unroll
         for (int i = 0; i < 4; i++) prod[i] = nan_to_zero(prod[i]);
-    }
-    const bool fits = c.k - c.kdone < kStage;
-    if (on && fits) c.buf[(c.k & (kStage - 1)) * kThreads] = make_float4(prod[0], prod[1], prod[2], prod[3]);
-    if (__any_sync(full, on && !fits)) {
-        float pn[NF];
+        if (__any_sync(full, over)) {
+            float pn[NF];
 #pragma unroll
-        for (int i = 0; i < NF; i++) pn[i] = prod[i];
-        sweep_accumulate_slow<NF>(c.acc, c.k, c.lane, pn, on && !fits);
+            for (int i = 0; i < NF; i++) pn[i] = prod[i];
+            sweep_accumulate_slow<NF>(c.acc, c.k, c.lane, pn, over);
+        }
     }
+    if (on && fits) c.buf[(c.k & (kStage - 1)) * kThreads] = make_float4(prod[0], prod[1], prod[2], prod[3]);
 }
 
 // Reduces the staged levels every lane of the warp has passed: [c.kdone, min over lanes of k).
@@ -161,7 +161,10 @@ __device__ __forceinline__ void sweep_emit(SweepCtx<NF>& c) {
         float o[NF];
 #pragma unroll
         for (int i = 0; i < NF; i++) o[i] = 0.f;
-        if (can) c.m.template edge<LAST>(c.pt, c.pb, c.rdpc, o);
+        // 1/thickness, the column weight and the below-surface mask enter as one factor
+        // (MASK_NONE: thr = -inf; level 0: thr = +inf, see kernel)
+        const float scale = (can && c.thr < c.psurf) ? c.rdpc * c.wv : 0.f;
+        if (can) c.m.template edge<LAST>(c.pt, c.pb, scale, o);
         sweep_stage<NF>(c, o, can);
         if (can) {
             c.pt = c.pb;
