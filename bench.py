@@ -225,17 +225,34 @@ def main():
 
     delp, area, fields = synth_device(torch, 1000 + rank, dev)
     cdim = NFINE // FACTOR
-    gathered = torch.empty((world, NFIELDS + 1, NTILE, KM, cdim, cdim), dtype=torch.float32, device=dev) if world > 1 else None
+    # N > 1: each rank's coarse outputs land in one contiguous buffer (no staging copy) and are
+    # all-gathered asynchronously -- the gather of step i runs under the kernel of step i + 1
+    # (double-buffered); the last one is waited for inside the timed region.
+    nbuf = 2
+    mine = [torch.empty((NFIELDS + 1, NTILE, KM, cdim, cdim), dtype=torch.float32, device=dev) for _ in range(nbuf)]
+    gathered = [torch.empty((world,) + tuple(mine[0].shape), dtype=torch.float32, device=dev) for _ in range(nbuf)] if world > 1 else None
+    pending = [None] * nbuf
+    counter = [0]
 
     def step():
-        outs, dco = core.pressure_coarsen(fields, delp, area, FACTOR, TOA, mask_mode="phalf", mode=mode)
+        i = counter[0] % nbuf
+        counter[0] += 1
+        if world > 1 and pending[i] is not None:
+            pending[i].wait()  # the gather that last used this buffer pair
+        outs, dco = core.pressure_coarsen(fields, delp, area, FACTOR, TOA, mask_mode="phalf", mode=mode, out=mine[i])
         if world > 1:  # C1: collect only the small coarse outputs
-            mine = torch.stack(list(outs) + [dco])
-            dist.all_gather_into_tensor(gathered, mine)
+            pending[i] = dist.all_gather_into_tensor(gathered[i], mine[i], async_op=True)
         return outs, dco
+
+    def drain():
+        for i in range(nbuf):
+            if pending[i] is not None:
+                pending[i].wait()
+                pending[i] = None
 
     for _ in range(args.warmup):
         step()
+    drain()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -244,10 +261,14 @@ def main():
         sampler.start()
         time.sleep(0.3)
     torch.cuda.synchronize()
+    if world > 1:  # rank 0 slept while the sampler started: line the ranks up again before timing
+        dist.barrier()
+        torch.cuda.synchronize()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     for _ in range(args.steps):
         step()
+    drain()
     ev1.record()
     torch.cuda.synchronize()
     if world > 1:
@@ -331,7 +352,7 @@ def main():
         "config": {"workload": "C384->C48 pressure-level fv_core A-grid (delp + W,T,ua,va): 6 tiles x 79 levels x "
                                "384 x 384 fp32, f=8, kord=1, iv=1, extrapolate=False, fused kernel",
                    "arithmetic_mode": args.mode, "l2": "inputs (1.42 GB) larger than L2, no flush needed",
-                   "per_rank": "one synthetic timestep per GPU (weak)", "collective": "NCCL all_gather of coarse outputs" if world > 1 else "none"},
+                   "per_rank": "one synthetic timestep per GPU (weak)", "collective": "NCCL all_gather of the coarse outputs (21.8 MB/rank), asynchronous: overlaps the next step" if world > 1 else "none"},
         "clocks": clocks,
         "other_mode": {"arithmetic_mode": "exact" if args.mode == "fast" else "fast", "kernel_ms": other_ms},
         "e2e": e2e,

@@ -13,7 +13,7 @@ F32, F64 = 0, 1
 OP_SUM, OP_MEAN, OP_MIN, OP_MAX, OP_MEDIAN, OP_MODE = range(6)
 MASK_NONE, MASK_PHALF, MASK_PFULL = 0, 1, 2
 EXACT, FAST = 0, 1
-EW_MUL, EW_WHERE, EW_WHERE_NOT, EW_SELECT, EW_FILLNA, EW_MIN_SCALAR = range(6)
+EW_MUL, EW_WHERE, EW_WHERE_NOT, EW_SELECT, EW_FILLNA, EW_MIN_SCALAR, EW_DIFF_OVER = range(7)
 CMP_ISCLOSE, CMP_LT, CMP_GT = range(3)
 SEQ_WINDOW = 2
 MAX_FIELDS = 16
@@ -24,7 +24,7 @@ EXPORTS = [
     "b200cs_pressure_at_interface", "b200cs_mappm_workspace_bytes", "b200cs_mappm",
     "b200cs_pressure_coarsen", "b200cs_mask_weights", "b200cs_surface_pressure", "b200cs_blending_weights",
     "b200cs_blend", "b200cs_hydrostatic_balance", "b200cs_elementwise", "b200cs_compare_scalar",
-    "b200cs_dominant_mask",
+    "b200cs_dominant_mask", "b200cs_pressure_at_midpoint_log", "b200cs_exposed_area_weights",
 ]
 
 _lib = None
@@ -71,6 +71,8 @@ def load():
     lib.b200cs_elementwise.argtypes = [i32, vp, vp, vp, vp, i32, i64, dbl, vp]
     lib.b200cs_compare_scalar.argtypes = [i32, vp, i32, dbl, dbl, dbl, vp, vp, i64, vp]
     lib.b200cs_dominant_mask.argtypes = [vp, vp, i32, i64, i64, i64, i32, dbl, dbl, vp, vp, vp]
+    lib.b200cs_pressure_at_midpoint_log.argtypes = [vp, vp, i32, i64, i32, i64, dbl, vp]
+    lib.b200cs_exposed_area_weights.argtypes = [vp, vp, i32, vp, i32, vp, i64, i32, i64, i64, i32, vp]
     lib.b200cs_hydrostatic_balance.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i64, i32, i64, dbl, dbl, dbl, dbl, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)

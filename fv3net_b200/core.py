@@ -322,7 +322,8 @@ def mask_weights(weights, p_coarse_on_fine, phalf_fine, mask_mode="phalf"):
 
 
 def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.0, mask_mode="phalf",
-                     edge_lines=False, iv=1, kord=1, mode=EXACT, return_delp_coarse=True, seq_window=False):
+                     edge_lines=False, iv=1, kord=1, mode=EXACT, return_delp_coarse=True, seq_window=False,
+                     out=None):
     """Fused pressure-level coarse-graining (one pass over the fine data).
 
     Equivalent to regrid_to_area_weighted_pressure + weighted_block_average with the masked
@@ -334,6 +335,8 @@ def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.
     edge_lines: windows are 1 x f (the rows are the kept lines of a D-grid wind component).
     seq_window: the window axis was not the contiguous axis of the reference's arrays (v lines are
     gathered columns), so sums follow numpy's sequential order for strided reductions.
+    out: optional preallocated device tensor ``[nfields + 1, B, km, cy, cx]`` that receives the
+    coarse fields and, last, the coarse delp (the returned tensors are views of it).
     Returns (list of coarse fields ``[B, km, cy, cx]``, coarse delp or None)."""
     f = int(coarsening_factor)
     was_np = not isinstance(delp, torch.Tensor)
@@ -371,8 +374,15 @@ def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.
     cy, cx = ny // fy, nx // f
     wdt = w.dtype
     cdt = _promote(d, w)
-    outs = [torch.empty((nb0, km, cy, cx), dtype=wdt, device=d.device) for _ in fs]
-    dco = torch.empty((nb0, km, cy, cx), dtype=cdt, device=d.device) if return_delp_coarse else None
+    if out is not None:
+        if (tuple(out.shape) != (len(fs) + 1, nb0, km, cy, cx) or out.dtype != wdt or cdt != wdt
+                or not out.is_contiguous() or out.device != d.device):
+            raise ValueError("pressure_coarsen: out must be a contiguous [nfields + 1, B, km, cy, cx] device tensor "
+                             "of the weights' dtype")
+        outs, dco = [out[i] for i in range(len(fs))], out[len(fs)]
+    else:
+        outs = [torch.empty((nb0, km, cy, cx), dtype=wdt, device=d.device) for _ in fs]
+        dco = torch.empty((nb0, km, cy, cx), dtype=cdt, device=d.device) if return_delp_coarse else None
     lib = _lib.load()
     rc = lib.b200cs_pressure_coarsen(
         len(fs), _lib.ptrarr([x.data_ptr() for x in fs]), _DT[fdt], _lib.i64arr(fs[0].stride()[:3] if fs else (0, 0, 0)),

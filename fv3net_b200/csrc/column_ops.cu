@@ -95,6 +95,40 @@ __global__ void hydrostatic_kernel(const T* __restrict__ dz_in, const T* __restr
     phis_out[i] = grav * (h + s);
 }
 
+
+// pressure_at_midpoint_log (vertically_dependent.py:153-179): delp / diff(log(p_interface))
+template <typename T>
+__global__ void midpoint_log_kernel(const T* __restrict__ delp, T* __restrict__ out, int64_t nb, int km, int64_t ncol,
+                                    T toa) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nb * ncol) return;
+    const int64_t b = i / ncol, c = i % ncol;
+    const int64_t sb = (int64_t)km * ncol;
+    T p = toa, lp = log(toa);
+    for (int k = 0; k < km; k++) {
+        const T d = delp[b * sb + k * ncol + c];
+        p = p + nan_to_zero(d);
+        const T ln = log(p);
+        out[b * sb + k * ncol + c] = d / (ln - lp);
+        lp = ln;
+    }
+}
+
+// Grid.area_above_fine_surface (workflows/fine_res_budget/budget/budgets.py:62-77), the fine-size
+// part: out[b, k, y, x] = pfull_coarse[b, k, y/f, x/f] <= ps[b, y, x] ? area[b, y, x] : 0
+template <typename TP, typename TA>
+__global__ void exposed_area_kernel(const TP* __restrict__ pfull_c, const TP* __restrict__ ps,
+                                    const TA* __restrict__ area, TA* __restrict__ out, int64_t nb, int km, int64_t ny,
+                                    int64_t nx, int f) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nb * km * ny * nx) return;
+    const int64_t x = i % nx, y = (i / nx) % ny, k = (i / (nx * ny)) % km, b = i / (nx * ny * km);
+    const int64_t cy = ny / f, cx = nx / f;
+    const TP pc = pfull_c[((b * km + k) * cy + y / f) * cx + x / f];
+    const int64_t col = (b * ny + y) * nx + x;
+    out[i] = (pc <= ps[col]) ? area[col] : TA(0);
+}
+
 inline unsigned blocks_for(int64_t n) { return (unsigned)((n + 255) / 256); }
 
 }  // namespace b200cs
@@ -170,6 +204,44 @@ int b200cs_hydrostatic_balance(const void* dz, const void* phis, const void* tem
             (const double*)dz, (const double*)phis, (const double*)temperature, (const double*)sphum, (const double*)delp,
             (double*)dz_out, (double*)phis_out, nb, km, ncol, toa_pressure, gravity, rdgas, zvir);
     return check_launch("hydrostatic_balance");
+}
+
+int b200cs_pressure_at_midpoint_log(const void* delp, void* out, int dtype, int64_t nb, int km, int64_t ncol,
+                                    double toa_pressure, void* stream) {
+    B200CS_REQUIRE(delp && out, "pressure_at_midpoint_log: NULL pointer");
+    B200CS_REQUIRE(nb >= 0 && km >= 1 && ncol >= 0, "pressure_at_midpoint_log: bad extents");
+    B200CS_REQUIRE(dtype == B200CS_F32 || dtype == B200CS_F64, "pressure_at_midpoint_log: bad dtype %d", dtype);
+    if (nb * ncol == 0) return B200CS_OK;
+    cudaStream_t st = as_stream(stream);
+    if (dtype == B200CS_F32)
+        midpoint_log_kernel<float><<<blocks_for(nb * ncol), 256, 0, st>>>((const float*)delp, (float*)out, nb, km, ncol,
+                                                                         (float)toa_pressure);
+    else
+        midpoint_log_kernel<double><<<blocks_for(nb * ncol), 256, 0, st>>>((const double*)delp, (double*)out, nb, km, ncol,
+                                                                          toa_pressure);
+    return check_launch("pressure_at_midpoint_log");
+}
+
+int b200cs_exposed_area_weights(const void* pfull_coarse, const void* ps_fine, int p_dtype, const void* area,
+                                int a_dtype, void* out, int64_t nb, int km, int64_t ny, int64_t nx, int factor,
+                                void* stream) {
+    B200CS_REQUIRE(pfull_coarse && ps_fine && area && out, "exposed_area_weights: NULL pointer");
+    B200CS_REQUIRE(factor >= 1 && ny % factor == 0 && nx % factor == 0, "exposed_area_weights: factor %d must divide the extents", factor);
+    B200CS_REQUIRE((p_dtype == B200CS_F32 || p_dtype == B200CS_F64) && (a_dtype == B200CS_F32 || a_dtype == B200CS_F64),
+                   "exposed_area_weights: bad dtype");
+    const int64_t n = nb * km * ny * nx;
+    if (n <= 0) return B200CS_OK;
+    cudaStream_t st = as_stream(stream);
+    const unsigned g = blocks_for(n);
+    if (p_dtype == B200CS_F32 && a_dtype == B200CS_F32)
+        exposed_area_kernel<float, float><<<g, 256, 0, st>>>((const float*)pfull_coarse, (const float*)ps_fine, (const float*)area, (float*)out, nb, km, ny, nx, factor);
+    else if (p_dtype == B200CS_F64 && a_dtype == B200CS_F32)
+        exposed_area_kernel<double, float><<<g, 256, 0, st>>>((const double*)pfull_coarse, (const double*)ps_fine, (const float*)area, (float*)out, nb, km, ny, nx, factor);
+    else if (p_dtype == B200CS_F32 && a_dtype == B200CS_F64)
+        exposed_area_kernel<float, double><<<g, 256, 0, st>>>((const float*)pfull_coarse, (const float*)ps_fine, (const double*)area, (double*)out, nb, km, ny, nx, factor);
+    else
+        exposed_area_kernel<double, double><<<g, 256, 0, st>>>((const double*)pfull_coarse, (const double*)ps_fine, (const double*)area, (double*)out, nb, km, ny, nx, factor);
+    return check_launch("exposed_area_weights");
 }
 
 }  // extern "C"

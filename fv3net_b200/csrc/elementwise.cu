@@ -27,7 +27,9 @@ __global__ void elementwise_kernel(int op, const T* __restrict__ a, const T* __r
         case B200CS_EW_WHERE_NOT: r = mask[i] ? s : a[i]; break;
         case B200CS_EW_SELECT: r = mask[i] ? a[i] : b[i]; break;
         case B200CS_EW_FILLNA: { const T v = a[i]; r = (v != v) ? s : v; break; }
-        default: { const T v = a[i]; r = (v < s) ? v : s; break; }  // B200CS_EW_MIN_SCALAR
+        case B200CS_EW_DIFF_OVER: r = (a[i] - b[i]) / s; break;
+        case B200CS_EW_MIN_SCALAR: { const T v = a[i]; r = (v < s) ? v : s; break; }
+        default: r = a[i]; break;
     }
     out[i] = r;
 }
@@ -71,11 +73,11 @@ extern "C" {
 
 int b200cs_elementwise(int op, const void* a, const void* b, const uint8_t* mask, void* out, int dtype, int64_t n,
                        double scalar, void* stream) {
-    B200CS_REQUIRE(op >= B200CS_EW_MUL && op <= B200CS_EW_MIN_SCALAR, "elementwise: unknown op %d", op);
+    B200CS_REQUIRE(op >= B200CS_EW_MUL && op <= B200CS_EW_DIFF_OVER, "elementwise: unknown op %d", op);
     B200CS_REQUIRE(a && out, "elementwise: NULL pointer");
     B200CS_REQUIRE(dtype == B200CS_F32 || dtype == B200CS_F64, "elementwise: bad dtype %d", dtype);
     B200CS_REQUIRE(n >= 0, "elementwise: bad extent");
-    if (op == B200CS_EW_MUL || op == B200CS_EW_SELECT) B200CS_REQUIRE(b, "elementwise: op %d needs b", op);
+    if (op == B200CS_EW_MUL || op == B200CS_EW_SELECT || op == B200CS_EW_DIFF_OVER) B200CS_REQUIRE(b, "elementwise: op %d needs b", op);
     if (op == B200CS_EW_WHERE || op == B200CS_EW_WHERE_NOT || op == B200CS_EW_SELECT)
         B200CS_REQUIRE(mask, "elementwise: op %d needs a mask", op);
     if (n == 0) return B200CS_OK;

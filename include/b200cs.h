@@ -231,6 +231,16 @@ int b200cs_mask_weights(const void* w, int w_dtype, const void* p_coarse, const 
  *   and phis adjusted to keep the model-top height of (dz, phis)
  *   (height_at_interface :69-98, dz_and_top_to_phis :182-186); phis [nb, ncol].
  */
+/* pressure_at_midpoint_log (VCM/calc/thermo/vertically_dependent.py:153-179) of contiguous
+ * [nb, km, ncol]; and the fine-size half of Grid.area_above_fine_surface
+ * (workflows/fine_res_budget/budget/budgets.py:62-77): out[nb, km, ny, nx] =
+ * pfull_coarse[nb, km, ny/f, nx/f] <= ps_fine[nb, ny, nx] ? area[nb, ny, nx] : 0 (block-summed by
+ * b200cs_block_reduce afterwards). */
+int b200cs_pressure_at_midpoint_log(const void* delp, void* out, int dtype, int64_t nb, int km,
+                                    int64_t ncol, double toa_pressure, void* stream);
+int b200cs_exposed_area_weights(const void* pfull_coarse, const void* ps_fine, int p_dtype,
+                                const void* area, int a_dtype, void* out, int64_t nb, int km,
+                                int64_t ny, int64_t nx, int factor, void* stream);
 int b200cs_surface_pressure(const void* delp, int dtype, const int64_t stride[2], void* ps,
                             int64_t nb, int km, int64_t ncol, double toa_pressure, void* stream);
 int b200cs_blending_weights(const void* delp_coarse, const void* ps_min, void* out, int dtype,
@@ -262,7 +272,8 @@ enum {
     B200CS_EW_WHERE_NOT = 2,
     B200CS_EW_SELECT = 3,
     B200CS_EW_FILLNA = 4,
-    B200CS_EW_MIN_SCALAR = 5
+    B200CS_EW_MIN_SCALAR = 5,
+    B200CS_EW_DIFF_OVER = 6 /* (a - b) / scalar: budget storage terms, budgets.py:80-85 */
 };
 enum { B200CS_CMP_ISCLOSE = 0, B200CS_CMP_LT = 1, B200CS_CMP_GT = 2 };
 int b200cs_elementwise(int op, const void* a, const void* b, const uint8_t* mask, void* out,
