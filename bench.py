@@ -202,6 +202,9 @@ def main():
     ap.add_argument("--mode", default="fast", choices=["exact", "fast"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
+                    help="N>1: 'peer' = the coarsening kernel stores its coarse outputs into every rank's gather "
+                         "buffer over NVLink peer memory (fused all-gather); 'nccl' = asynchronous NCCL all_gather")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -229,14 +232,28 @@ def main():
     # all-gathered asynchronously -- the gather of step i runs under the kernel of step i + 1
     # (double-buffered); the last one is waited for inside the timed region.
     nbuf = 2
-    mine = [torch.empty((NFIELDS + 1, NTILE, KM, cdim, cdim), dtype=torch.float32, device=dev) for _ in range(nbuf)]
-    gathered = [torch.empty((world,) + tuple(mine[0].shape), dtype=torch.float32, device=dev) for _ in range(nbuf)] if world > 1 else None
+    use_peer = world > 1 and args.collective == "peer" and mode == core.FAST
     pending = [None] * nbuf
     counter = [0]
+    if use_peer:
+        # fused compute + all-gather: every rank's kernel writes slot `rank` of every rank's
+        # symmetric-memory buffer while it computes; a device-side barrier per step orders readers
+        from fv3net_b200.gather import CoarseGather
+
+        gath = [CoarseGather(NFIELDS, NTILE, KM, cdim, cdim, dev) for _ in range(nbuf)]
+        local = torch.empty((NFIELDS + 1, NTILE, KM, cdim, cdim), dtype=torch.float32, device=dev)
+    else:
+        mine = [torch.empty((NFIELDS + 1, NTILE, KM, cdim, cdim), dtype=torch.float32, device=dev) for _ in range(nbuf)]
+        gathered = [torch.empty((world,) + tuple(mine[0].shape), dtype=torch.float32, device=dev) for _ in range(nbuf)] if world > 1 else None
 
     def step():
         i = counter[0] % nbuf
         counter[0] += 1
+        if use_peer:
+            outs, dco = core.pressure_coarsen(fields, delp, area, FACTOR, TOA, mask_mode="phalf", mode=mode, out=local,
+                                              peer_ptrs=gath[i].peer_ptrs)
+            gath[i].barrier()  # all writers of buffer i are done: gath[i].buffer holds every rank's outputs
+            return outs, dco
         if world > 1 and pending[i] is not None:
             pending[i].wait()  # the gather that last used this buffer pair
         outs, dco = core.pressure_coarsen(fields, delp, area, FACTOR, TOA, mask_mode="phalf", mode=mode, out=mine[i])
@@ -254,6 +271,12 @@ def main():
         step()
     drain()
     torch.cuda.synchronize()
+    if use_peer:  # once, untimed: the peer-written buffer equals an NCCL all_gather of the same outputs
+        ref = torch.empty((world,) + tuple(local.shape), dtype=torch.float32, device=dev)
+        dist.all_gather_into_tensor(ref, local)
+        got = gath[(counter[0] - 1) % nbuf].buffer
+        assert torch.equal(torch.nan_to_num(ref), torch.nan_to_num(got)), "fused gather differs from NCCL all_gather"
+        del ref
     if world > 1:
         dist.barrier()
     sampler = ClockSampler(local_rank)
@@ -352,7 +375,7 @@ def main():
         "config": {"workload": "C384->C48 pressure-level fv_core A-grid (delp + W,T,ua,va): 6 tiles x 79 levels x "
                                "384 x 384 fp32, f=8, kord=1, iv=1, extrapolate=False, fused kernel",
                    "arithmetic_mode": args.mode, "l2": "inputs (1.42 GB) larger than L2, no flush needed",
-                   "per_rank": "one synthetic timestep per GPU (weak)", "collective": "NCCL all_gather of the coarse outputs (21.8 MB/rank), asynchronous: overlaps the next step" if world > 1 else "none"},
+                   "per_rank": "one synthetic timestep per GPU (weak)", "collective": ("none" if world == 1 else "fused: the coarsening kernel stores its coarse outputs (21.8 MB/rank) into every rank's gather buffer over NVLink peer memory, one device-side barrier per step" if use_peer else "NCCL all_gather of the coarse outputs (21.8 MB/rank), asynchronous: overlaps the next step")},
         "clocks": clocks,
         "other_mode": {"arithmetic_mode": "exact" if args.mode == "fast" else "fast", "kernel_ms": other_ms},
         "e2e": e2e,

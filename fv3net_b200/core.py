@@ -323,7 +323,7 @@ def mask_weights(weights, p_coarse_on_fine, phalf_fine, mask_mode="phalf"):
 
 def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.0, mask_mode="phalf",
                      edge_lines=False, iv=1, kord=1, mode=EXACT, return_delp_coarse=True, seq_window=False,
-                     out=None):
+                     out=None, peer_ptrs=None):
     """Fused pressure-level coarse-graining (one pass over the fine data).
 
     Equivalent to regrid_to_area_weighted_pressure + weighted_block_average with the masked
@@ -337,6 +337,9 @@ def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.
     gathered columns), so sums follow numpy's sequential order for strided reductions.
     out: optional preallocated device tensor ``[nfields + 1, B, km, cy, cx]`` that receives the
     coarse fields and, last, the coarse delp (the returned tensors are views of it).
+    peer_ptrs: device pointers of this rank's slot in every peer's gather buffer
+    (fv3net_b200.gather.CoarseGather.peer_ptrs): the kernel also stores the coarse outputs there
+    over NVLink (fused all-gather; FAST mode, fp32, 8 x 8 windows only).
     Returns (list of coarse fields ``[B, km, cy, cx]``, coarse delp or None)."""
     f = int(coarsening_factor)
     was_np = not isinstance(delp, torch.Tensor)
@@ -384,11 +387,17 @@ def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.
         outs = [torch.empty((nb0, km, cy, cx), dtype=wdt, device=d.device) for _ in fs]
         dco = torch.empty((nb0, km, cy, cx), dtype=cdt, device=d.device) if return_delp_coarse else None
     lib = _lib.load()
-    rc = lib.b200cs_pressure_coarsen(
-        len(fs), _lib.ptrarr([x.data_ptr() for x in fs]), _DT[fdt], _lib.i64arr(fs[0].stride()[:3] if fs else (0, 0, 0)),
-        d.data_ptr(), _DT[d.dtype], _lib.i64arr(d.stride()[:3]), w.data_ptr(), _DT[wdt], _lib.i64arr(w.stride()[:2]),
-        _lib.ptrarr([o.data_ptr() for o in outs]), dco.data_ptr() if dco is not None else None,
-        nb0, km, ny, nx, fy, f, float(toa_pressure), _MASK[mask_mode], int(iv), int(kord), int(mode) | (_lib.SEQ_WINDOW if seq_window else 0), _stream())
+    args = (len(fs), _lib.ptrarr([x.data_ptr() for x in fs]), _DT[fdt], _lib.i64arr(fs[0].stride()[:3] if fs else (0, 0, 0)),
+            d.data_ptr(), _DT[d.dtype], _lib.i64arr(d.stride()[:3]), w.data_ptr(), _DT[wdt], _lib.i64arr(w.stride()[:2]),
+            _lib.ptrarr([o.data_ptr() for o in outs]), dco.data_ptr() if dco is not None else None,
+            nb0, km, ny, nx, fy, f, float(toa_pressure), _MASK[mask_mode], int(iv), int(kord),
+            int(mode) | (_lib.SEQ_WINDOW if seq_window else 0))
+    if peer_ptrs:
+        nws = lib.b200cs_pressure_coarsen_gather_workspace_bytes(nb0, ny)
+        ws = torch.empty(max(nws, 4), dtype=torch.uint8, device=d.device)
+        rc = lib.b200cs_pressure_coarsen_gather(*args, len(peer_ptrs), _lib.ptrarr(peer_ptrs), ws.data_ptr(), nws, _stream())
+    else:
+        rc = lib.b200cs_pressure_coarsen(*args, _stream())
     _lib.check(rc, "pressure_coarsen")
     if was_np:
         return [o.cpu().numpy() for o in outs], (dco.cpu().numpy() if dco is not None else None)

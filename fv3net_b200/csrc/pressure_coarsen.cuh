@@ -29,6 +29,16 @@ namespace b200cs {
 constexpr int kTileX = 32, kTileY = 8, kThreads = kTileX * kTileY;
 constexpr int kKC = 4;  // levels handled between two CTA barriers
 
+// Peer-mapped copies of the coarse outputs (fused all-gather over NVLink): slot layout
+// [nfields + 1][nb0, km, cy, cx], the coarse delp last.
+struct PeerOut {
+    int n;
+    int nfields;
+    int64_t field_elems;
+    int* counters;  // [nb0 * gridDim.y], zeroed before the launch: CTAs finished per coarse row of tiles
+    float* base[8];
+};
+
 template <int NF>
 struct FieldPtrs {
     const void* in[NF];
@@ -274,6 +284,9 @@ struct PcArgs {
     int mask_mode, iv, kord;
     cudaStream_t st;
     int seq;  // B200CS_SEQ_WINDOW
+    int npeer = 0;                 // b200cs_pressure_coarsen_gather: peer-mapped destinations
+    void* const* peer = nullptr;   // [npeer] this rank's slot in each peer's gathered buffer
+    int* counters = nullptr;       // workspace of the gather (see PeerOut)
 };
 
 template <int MODE, int NF, typename TP, typename TW, int FX>

@@ -14,13 +14,15 @@ int pc_fast_entry(const PcArgs&);
 
 using namespace b200cs;
 
-extern "C" int b200cs_pressure_coarsen(int nfields, const void* const* fields, int field_dtype,
-                                       const int64_t field_stride[3], const void* delp, int p_dtype,
-                                       const int64_t delp_stride[3], const void* w, int w_dtype,
-                                       const int64_t w_stride[2], void* const* out, void* delp_coarse,
-                                       int64_t nb0, int km, int64_t ny, int64_t nx, int fy, int fx,
-                                       double toa_pressure, int mask_mode, int iv, int kord, int mode,
-                                       void* stream) {
+extern "C" int64_t b200cs_pressure_coarsen_gather_workspace_bytes(int64_t nb0, int64_t ny) {
+    return (int64_t)sizeof(int) * nb0 * ((ny + kTileY - 1) / kTileY);
+}
+
+static int pc_dispatch(int nfields, const void* const* fields, int field_dtype, const int64_t field_stride[3],
+                       const void* delp, int p_dtype, const int64_t delp_stride[3], const void* w, int w_dtype,
+                       const int64_t w_stride[2], void* const* out, void* delp_coarse, int64_t nb0, int km, int64_t ny,
+                       int64_t nx, int fy, int fx, double toa_pressure, int mask_mode, int iv, int kord, int mode,
+                       int npeers, void* const* peer_out, void* workspace, int64_t workspace_bytes, void* stream) {
     B200CS_REQUIRE(nfields >= 0 && nfields <= B200CS_MAX_FIELDS, "pressure_coarsen: nfields must be 0..%d", B200CS_MAX_FIELDS);
     B200CS_REQUIRE(delp && w && delp_stride && w_stride, "pressure_coarsen: NULL argument");
     B200CS_REQUIRE(nfields == 0 || (fields && out && field_stride), "pressure_coarsen: NULL field arrays");
@@ -43,6 +45,19 @@ extern "C" int b200cs_pressure_coarsen(int nfields, const void* const* fields, i
     if (nb0 == 0) return B200CS_OK;
     PcArgs a{nfields, fields, field_dtype, field_stride, delp, delp_stride, w, w_stride, out, delp_coarse,
              nb0, km, ny, nx, fy, fx, toa_pressure, mask_mode, iv, kord, as_stream(stream), seq};
+    a.npeer = npeers;
+    a.peer = peer_out;
+    if (npeers > 0) {
+        B200CS_REQUIRE(npeers <= 8 && peer_out, "pressure_coarsen_gather: 1..8 peers");
+        for (int p = 0; p < npeers; p++) B200CS_REQUIRE(peer_out[p], "pressure_coarsen_gather: peer %d is NULL", p);
+        B200CS_REQUIRE(delp_coarse, "pressure_coarsen_gather: delp_coarse is part of the gathered slot");
+        if (!workspace || workspace_bytes < b200cs_pressure_coarsen_gather_workspace_bytes(nb0, ny))
+            return set_err(B200CS_EWORKSPACE, "pressure_coarsen_gather: workspace of %lld bytes needed",
+                           (long long)b200cs_pressure_coarsen_gather_workspace_bytes(nb0, ny));
+        a.counters = (int*)workspace;
+        if (mode != B200CS_FAST || !pc_fast_covers(a, field_dtype, p_dtype, w_dtype) || fy != fx)
+            return set_err(B200CS_EUNSUPPORTED, "pressure_coarsen_gather: only the FAST fp32 8x8 kernel (kord <= 3) scatters to peers");
+    }
     // with no fields the kernel still produces delp_coarse: run it on a dummy 1-field launch
     const void* dummy_in[1] = {delp};
     void* dummy_out[1] = {nullptr};
@@ -60,4 +75,29 @@ extern "C" int b200cs_pressure_coarsen(int nfields, const void* const* fields, i
     if (fx == 8) return pc_entry_fx8_m1(a, p_dtype, w_dtype);
     if (fx == 4) return pc_entry_fx4_m1(a, p_dtype, w_dtype);
     return pc_entry_fx2_m1(a, p_dtype, w_dtype);
+}
+
+extern "C" int b200cs_pressure_coarsen(int nfields, const void* const* fields, int field_dtype,
+                                       const int64_t field_stride[3], const void* delp, int p_dtype,
+                                       const int64_t delp_stride[3], const void* w, int w_dtype,
+                                       const int64_t w_stride[2], void* const* out, void* delp_coarse,
+                                       int64_t nb0, int km, int64_t ny, int64_t nx, int fy, int fx,
+                                       double toa_pressure, int mask_mode, int iv, int kord, int mode,
+                                       void* stream) {
+    return pc_dispatch(nfields, fields, field_dtype, field_stride, delp, p_dtype, delp_stride, w, w_dtype, w_stride, out,
+                       delp_coarse, nb0, km, ny, nx, fy, fx, toa_pressure, mask_mode, iv, kord, mode, 0, nullptr, nullptr, 0, stream);
+}
+
+extern "C" int b200cs_pressure_coarsen_gather(int nfields, const void* const* fields, int field_dtype,
+                                              const int64_t field_stride[3], const void* delp, int p_dtype,
+                                              const int64_t delp_stride[3], const void* w, int w_dtype,
+                                              const int64_t w_stride[2], void* const* out, void* delp_coarse,
+                                              int64_t nb0, int km, int64_t ny, int64_t nx, int fy, int fx,
+                                              double toa_pressure, int mask_mode, int iv, int kord, int mode,
+                                              int npeers, void* const* peer_out, void* workspace,
+                                              int64_t workspace_bytes, void* stream) {
+    if (npeers < 1) return set_err(B200CS_EINVAL, "pressure_coarsen_gather: npeers must be >= 1");
+    return pc_dispatch(nfields, fields, field_dtype, field_stride, delp, p_dtype, delp_stride, w, w_dtype, w_stride, out,
+                       delp_coarse, nb0, km, ny, nx, fy, fx, toa_pressure, mask_mode, iv, kord, mode, npeers, peer_out,
+                       workspace, workspace_bytes, stream);
 }

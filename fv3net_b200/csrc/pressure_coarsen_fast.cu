@@ -15,7 +15,7 @@ static bool use_v1() {
     return v;
 }
 int pc_fast_entry(const PcArgs& a) {
-    if (use_v1()) return a.fy == 8 ? launch_pc_fast_fields<8>(a) : launch_pc_fast_fields<1>(a);
+    if (use_v1() && a.npeer == 0) return a.fy == 8 ? launch_pc_fast_fields<8>(a) : launch_pc_fast_fields<1>(a);
     if (a.fy == 8) return launch_pc_sweep_fields<8>(a);
     return launch_pc_sweep_fields<1>(a);
 }

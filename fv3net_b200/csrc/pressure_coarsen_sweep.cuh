@@ -213,7 +213,7 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
                               const float* __restrict__ delp, int64_t ds0, int64_t dsl, int64_t dsy,
                               const float* __restrict__ w, int64_t ws0, int64_t wsy,
                               float* __restrict__ delp_coarse, int km, int64_t ny, int64_t nx, float toa,
-                              int mask_mode, int iv, int seq_i) {
+                              int mask_mode, int iv, int seq_i, const __grid_constant__ PeerOut peers, int first) {
     constexpr int FX = 8;
     const bool seq = seq_i != 0;
     constexpr int CW = kTileX / FX;   // cells per tile row
@@ -438,6 +438,51 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
             for (int i = 0; i < NF; i++) ((float*)fp.out[i])[o] = num[i] / den;
         }
     }
+
+    // ---------------- fused all-gather (b200cs_pressure_coarsen_gather) ----------------------
+    // The CTAs of one row of tiles (same blockIdx.y, b0) produce CH complete coarse rows.  The
+    // last of them to finish copies those rows -- contiguous cxN-float segments, read back through
+    // L2 -- into this rank's slot on every peer with 16-byte stores over NVLink: full-size
+    // packets instead of the 4-byte scattered stores of Phase C, no separate collective kernel.
+    if (peers.n > 0) {
+        __shared__ int s_last;
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) {
+            const int prev = atomicAdd(&peers.counters[b0 * gridDim.y + blockIdx.y], 1);
+            s_last = (prev == (int)gridDim.x - 1);
+        }
+        __syncthreads();
+        if (s_last) {
+            __threadfence();
+            const int64_t rows = CH;                       // coarse rows of this row of tiles
+            const int64_t cy0 = (int64_t)blockIdx.y * CH;
+            const bool vec = (cxN % 4 == 0);
+            const int64_t per_row = vec ? cxN / 4 : cxN;
+            const int64_t total = (int64_t)km * rows * per_row;
+#pragma unroll
+            for (int sl = 0; sl <= NF; sl++) {             // compile-time slot index: no local copy of fp
+                const float* src = sl < NF ? (const float*)fp.out[sl < NF ? sl : 0] : delp_coarse;
+                if (sl == NF && !(first == 0 && delp_coarse)) continue;
+                const int64_t slot = sl < NF ? (first + sl) : peers.nfields;
+                for (int64_t e = tid; e < total; e += kThreads) {
+                    const int64_t c = e % per_row;
+                    const int64_t r = (e / per_row) % rows;
+                    const int64_t k = e / (per_row * rows);
+                    if (cy0 + r >= cyN) continue;
+                    const int64_t o = ((b0 * km + k) * cyN + cy0 + r) * cxN;
+                    if (vec) {
+                        const float4 v = __ldcg(reinterpret_cast<const float4*>(src + o) + c);
+                        for (int p = 0; p < peers.n; p++)
+                            reinterpret_cast<float4*>(peers.base[p] + slot * peers.field_elems + o)[c] = v;
+                    } else {
+                        const float v = __ldcg(src + o + c);
+                        for (int p = 0; p < peers.n; p++) peers.base[p][slot * peers.field_elems + o + c] = v;
+                    }
+                }
+            }
+        }
+    }
 }
 
 template <int NF, int FY>
@@ -459,10 +504,20 @@ int launch_pc_sweep(const PcArgs& a, int first) {
     FieldPtrs<NF> fp;
     for (int i = 0; i < NF; i++) { fp.in[i] = a.fields[first + i]; fp.out[i] = a.out[first + i]; }
     dim3 grid((unsigned)((a.nx + kTileX - 1) / kTileX), (unsigned)((a.ny + kTileY - 1) / kTileY), (unsigned)a.nb0);
+    PeerOut po{};
+    po.n = a.npeer;
+    po.nfields = a.nfields;
+    po.field_elems = a.nb0 * a.km * (a.ny / FY) * (a.nx / 8);
+    po.counters = a.counters;
+    if (a.npeer > 0) {
+        cudaError_t em = cudaMemsetAsync(a.counters, 0, sizeof(int) * (size_t)grid.y * (size_t)a.nb0, a.st);
+        if (em != cudaSuccess) return set_err(B200CS_ECUDA, "pressure_coarsen_gather: cudaMemsetAsync: %s", cudaGetErrorString(em));
+    }
+    for (int p = 0; p < a.npeer && p < 8; p++) po.base[p] = (float*)a.peer[p];
     kern<<<grid, kThreads, smem, a.st>>>(fp, a.fstride[0], a.fstride[1], a.fstride[2], (const float*)a.delp,
                                          a.dstride[0], a.dstride[1], a.dstride[2], (const float*)a.w, a.wstride[0],
                                          a.wstride[1], first == 0 ? (float*)a.delp_coarse : nullptr, a.km, a.ny, a.nx,
-                                         (float)a.toa, a.mask_mode, a.iv, a.seq);
+                                         (float)a.toa, a.mask_mode, a.iv, a.seq, po, first);
     return check_launch("pressure_coarsen(fast)");
 }
 

@@ -204,6 +204,28 @@ int b200cs_pressure_coarsen(int nfields, const void* const* fields, int field_dt
                             void* stream);
 
 /*
+ * Fused compute + all-gather.  The same kernel as b200cs_pressure_coarsen (FAST mode, fp32, 8 x 8
+ * windows) additionally stores every coarse value into `npeers` (1..8) peer-mapped buffers as it
+ * is produced -- plain stores over NVLink peer memory, no separate collective and no SMs taken
+ * from the coarsening.  peer_out[p] points at THIS rank's slot inside rank p's gathered buffer;
+ * a slot is contiguous [nfields + 1][nb0, km, cy, cx] fp32 with the coarse delp last.  The caller
+ * maps the buffers (CUDA IPC / cuMem fabric handles; torch symmetric memory in the Python layer)
+ * and orders readers after the writers (a barrier after the kernel).  Replaces the NCCL
+ * all-gather of the coarse outputs of SURVEY.md 8e.  The copies are made by the last CTA of each
+ * row of tiles (complete coarse rows, 16-byte stores); `workspace` holds the per-row arrival
+ * counters (b200cs_pressure_coarsen_gather_workspace_bytes(nb0, ny) bytes, zeroed by the call).
+ */
+int64_t b200cs_pressure_coarsen_gather_workspace_bytes(int64_t nb0, int64_t ny);
+int b200cs_pressure_coarsen_gather(int nfields, const void* const* fields, int field_dtype,
+                                   const int64_t field_stride[3], const void* delp, int p_dtype,
+                                   const int64_t delp_stride[3], const void* w, int w_dtype,
+                                   const int64_t w_stride[2], void* const* out, void* delp_coarse,
+                                   int64_t nb0, int km, int64_t ny, int64_t nx, int fy, int fx,
+                                   double toa_pressure, int mask_mode, int iv, int kord, int mode,
+                                   int npeers, void* const* peer_out, void* workspace,
+                                   int64_t workspace_bytes, void* stream);
+
+/*
  * Below-surface weight mask for the unfused path and API parity with _mask_weights
  * (VCM/cubedsphere/regridz.py:200-220): out[b,k,col] = cond ? w[b,col] : 0 with
  *   PHALF: phalf_coarse_on_fine[b,k+1,col] < phalf_fine[b,km,col]

@@ -722,6 +722,29 @@ def area_above_fine_surface(delp_fine, delp_coarse, area, f):
     return coarsen_sum(w, f, f)
 
 
+def compute_recoarsened_budget_inputs(begin, middle, end, dt=900, f=8, first_moments=("T", "sphum", "vulcan_omega_coarse"),
+                                      second_moments=(("T", "vulcan_omega_coarse"), ("sphum", "vulcan_omega_coarse")),
+                                      storage_terms=("T", "sphum"), nthreads=1):
+    """budgets.py:217-294 on name -> [tile, z, y, x] mappings (the three ``step`` slices)."""
+    area, delp = middle["area_coarse"], middle["delp"]
+    delp_coarse = weighted_block_average(delp, area[:, None], f)
+    raw = {v: middle[v] for v in first_moments}
+    for a, b in second_moments:
+        raw[f"{a}_{b}"] = middle[a] * middle[b]
+    for v in storage_terms:
+        raw[f"{v}_storage"] = (end[v] - begin[v]) / dt
+    out = {}
+    for k, v in raw.items():
+        if v.ndim == delp.ndim:
+            out[k] = pressure_level_average(delp, delp_coarse, area[:, None], v, f, nthreads)
+        else:
+            out[k] = weighted_block_average(v, area, f)
+    out["delp"] = delp_coarse
+    out["exposed_area"] = area_above_fine_surface(delp, delp_coarse, middle["exposed_area_coarse"][:, None], f)
+    out["area"] = coarsen_sum(area, f, f)
+    return out
+
+
 # --------------------------------------------------------------------------------------
 # synthetic inputs of the reference regression test
 # (external/synth/synth/core.py:59-67,136; external/vcm/tests/test_coarsen_restarts.py:24-30)

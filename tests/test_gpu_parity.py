@@ -710,3 +710,56 @@ def test_sfc_data_realistic_vs_oracle(oracle, core, f):
     assert eq(simple["slmsk"], np.round(oracle.horizontal_block_reduce(ds["slmsk"], f, np.median)))
     with pytest.raises(ValueError, match="only supported versions"):
         sfc_data.coarse_grain_sfc_data(ds, area, f, version="other")
+
+
+# ------------------------------------------------------------------------------------------
+# N4: fine_res_budget re-coarse-graining (workflows/fine_res_budget/budget/budgets.py:49-117,217-294)
+# ------------------------------------------------------------------------------------------
+def test_budget_inputs_vs_oracle(core, oracle):
+    from fv3net_b200 import budget
+
+    rng = np.random.default_rng(51)
+    nb, km, n, f = 2, 10, 16, 8
+    delp = _synthetic_columns(rng, nb, km, n, np.float32)
+    shape = delp.shape
+    mid = {"delp": delp, "area_coarse": rng.uniform(0.5, 1, size=(nb, n, n)).astype(np.float32),
+           "exposed_area_coarse": rng.uniform(0.5, 1, size=(nb, n, n)).astype(np.float32),
+           "T": rng.uniform(200, 300, size=shape).astype(np.float32), "sphum": rng.uniform(0, 0.02, size=shape).astype(np.float32),
+           "vulcan_omega_coarse": rng.normal(size=shape).astype(np.float32),
+           "PRATEsfc": rng.uniform(0, 1, size=(nb, n, n)).astype(np.float32)}
+    begin = {k: (mid[k] + rng.normal(size=shape).astype(np.float32)) for k in ("T", "sphum")}
+    end = {k: (mid[k] + rng.normal(size=shape).astype(np.float32)) for k in ("T", "sphum")}
+    fm = ("T", "sphum", "vulcan_omega_coarse", "PRATEsfc")
+    got = budget.compute_recoarsened_budget_inputs(begin, mid, end, dt=900, factor=f, first_moments=fm)
+    exp = oracle.compute_recoarsened_budget_inputs(begin, mid, end, dt=900, f=f, first_moments=fm)
+    assert set(got) == set(exp)
+    for k in exp:
+        assert eq(got[k], exp[k]), k
+    assert got["exposed_area"].shape == (nb, km, n // f, n // f)
+    assert (got["exposed_area"][:, 0] == oracle.coarsen_sum(mid["exposed_area_coarse"], f, f)).all()  # top level: all exposed
+    assert (got["exposed_area"][:, -1] < got["exposed_area"][:, 0]).any()  # some fine columns end above the coarse surface
+    # a single-field call equals Grid.pressure_level_average
+    (one,), dco = budget.pressure_level_average(delp, mid["area_coarse"], [mid["T"]], f)
+    assert eq(one, exp["T"]) and eq(dco, exp["delp"])
+
+
+def test_fused_gather_slots_single_gpu(core):
+    """b200cs_pressure_coarsen_gather with two 'peers' that are plain local buffers: every slot
+    receives exactly the kernel's outputs (fields in order, coarse delp last)."""
+    rng = np.random.default_rng(61)
+    nb, km, n, f = 2, 12, 32, 8
+    delp = torch.as_tensor(_synthetic_columns(rng, nb, km, n, np.float32)).cuda()
+    area = torch.as_tensor(rng.uniform(0.5, 1, size=(nb, n, n)).astype(np.float32)).cuda()
+    fields = [torch.as_tensor(rng.normal(size=(nb, km, n, n)).astype(np.float32)).cuda() for _ in range(5)]  # 4 + 1 launches
+    ref, dref = core.pressure_coarsen(fields, delp, area, f, mode=core.FAST)
+    slots = torch.zeros((2, len(fields) + 1, nb, km, n // f, n // f), dtype=torch.float32, device="cuda")
+    outs, dco = core.pressure_coarsen(fields, delp, area, f, mode=core.FAST,
+                                      peer_ptrs=[slots[0].data_ptr(), slots[1].data_ptr()])
+    torch.cuda.synchronize()
+    exp = torch.stack(list(ref) + [dref])
+    for s in range(2):
+        assert torch.equal(torch.nan_to_num(slots[s]), torch.nan_to_num(exp))
+    assert all(torch.equal(torch.nan_to_num(a), torch.nan_to_num(b)) for a, b in zip(outs, ref))
+    from fv3net_b200._lib import B200csError
+    with pytest.raises(B200csError, match="only the FAST"):
+        core.pressure_coarsen(fields, delp, area, f, mode=core.EXACT, peer_ptrs=[slots[0].data_ptr()])
