@@ -26,6 +26,7 @@ EXPORTS = [
     "b200cs_blend", "b200cs_hydrostatic_balance", "b200cs_elementwise", "b200cs_compare_scalar",
     "b200cs_dominant_mask", "b200cs_pressure_at_midpoint_log", "b200cs_exposed_area_weights",
     "b200cs_pressure_coarsen_gather", "b200cs_pressure_coarsen_gather_workspace_bytes",
+    "b200cs_pressure_coarsen_wide", "b200cs_pressure_coarsen_wide_workspace_bytes",
 ]
 
 _lib = None
@@ -69,6 +70,10 @@ def load():
                                                    i64, i64, i32, i32, dbl, i32, i32, i32, i32, i32, pvp, vp, i64, vp]
     lib.b200cs_pressure_coarsen_gather_workspace_bytes.argtypes = [i64, i64]
     lib.b200cs_pressure_coarsen_gather_workspace_bytes.restype = i64
+    lib.b200cs_pressure_coarsen_wide.argtypes = [i32, pvp, p64, vp, p64, vp, p64, pvp, vp, i64, i32, i64, i64, i32, dbl,
+                                                 i32, i32, i32, vp, i64, vp]
+    lib.b200cs_pressure_coarsen_wide_workspace_bytes.argtypes = [i64, i32, i64, i64, i32]
+    lib.b200cs_pressure_coarsen_wide_workspace_bytes.restype = i64
     lib.b200cs_mask_weights.argtypes = [vp, i32, vp, vp, i32, vp, i64, i64, i64, i32, vp]
     lib.b200cs_surface_pressure.argtypes = [vp, i32, p64, vp, i64, i32, i64, dbl, vp]
     lib.b200cs_blending_weights.argtypes = [vp, vp, vp, i32, i64, i32, i64, dbl, dbl, vp]
@@ -81,7 +86,8 @@ def load():
     lib.b200cs_hydrostatic_balance.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i64, i32, i64, dbl, dbl, dbl, dbl, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
-        if name not in ("b200cs_last_error", "b200cs_mappm_workspace_bytes", "b200cs_pressure_coarsen_gather_workspace_bytes"):
+        if name not in ("b200cs_last_error", "b200cs_mappm_workspace_bytes", "b200cs_pressure_coarsen_gather_workspace_bytes",
+                        "b200cs_pressure_coarsen_wide_workspace_bytes"):
             fn.restype = i32
     _lib = lib
     return lib

@@ -377,6 +377,17 @@ def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.
     cy, cx = ny // fy, nx // f
     wdt = w.dtype
     cdt = _promote(d, w)
+    if f not in (2, 4, 8):  # a coarse cell wider than one CTA tile (C3072 -> C48 is factor 64)
+        if edge_lines or peer_ptrs or out is not None:
+            raise ValueError("pressure_coarsen: edge lines / gather buffers need a factor of 2, 4 or 8")
+        all_f32 = fdt == torch.float32 and d.dtype == torch.float32 and wdt == torch.float32
+        if mode == FAST and all_f32 and f in (16, 32, 64) and int(kord) <= 3 and fs:
+            outs, dco = _pressure_coarsen_wide(fs, d, w, f, toa_pressure, mask_mode, iv, kord, return_delp_coarse)
+        else:
+            outs, dco = _pressure_coarsen_unfused(fs, d, w, f, toa_pressure, mask_mode, iv, kord)
+        if was_np:
+            return [o.cpu().numpy() for o in outs], (dco.cpu().numpy() if dco is not None else None)
+        return outs, dco
     if out is not None:
         if (tuple(out.shape) != (len(fs) + 1, nb0, km, cy, cx) or out.dtype != wdt or cdt != wdt
                 or not out.is_contiguous() or out.device != d.device):
@@ -401,6 +412,49 @@ def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.
     _lib.check(rc, "pressure_coarsen")
     if was_np:
         return [o.cpu().numpy() for o in outs], (dco.cpu().numpy() if dco is not None else None)
+    return outs, dco
+
+
+def _pressure_coarsen_wide(fs, d, w, f, toa_pressure, mask_mode, iv, kord, return_delp_coarse):
+    """b200cs_pressure_coarsen_wide: FAST arithmetic, fp32, factor 16 / 32 / 64."""
+    nb0, km, ny, nx = d.shape
+    cy, cx = ny // f, nx // f
+    lib = _lib.load()
+    outs = [torch.empty((nb0, km, cy, cx), dtype=torch.float32, device=d.device) for _ in fs]
+    dco = torch.empty((nb0, km, cy, cx), dtype=torch.float32, device=d.device) if return_delp_coarse else None
+    nws = lib.b200cs_pressure_coarsen_wide_workspace_bytes(nb0, km, ny, nx, f)
+    ws = torch.empty(max(nws, 4), dtype=torch.uint8, device=d.device)
+    rc = lib.b200cs_pressure_coarsen_wide(
+        len(fs), _lib.ptrarr([x.data_ptr() for x in fs]), _lib.i64arr(fs[0].stride()[:3]), d.data_ptr(),
+        _lib.i64arr(d.stride()[:3]), w.data_ptr(), _lib.i64arr(w.stride()[:2]), _lib.ptrarr([o.data_ptr() for o in outs]),
+        dco.data_ptr() if dco is not None else None, nb0, km, ny, nx, f, float(toa_pressure), _MASK[mask_mode], int(iv),
+        int(kord), ws.data_ptr(), nws, _stream())
+    _lib.check(rc, "pressure_coarsen_wide")
+    return outs, dco
+
+
+def _pressure_coarsen_unfused(fs, d, w, f, toa_pressure, mask_mode, iv, kord):
+    """Any factor, any dtype, every kord: the reference's own chain of operators
+    (cubedsphere/regridz.py:31-220 + coarsen_restarts.py:528-534), one kernel each, bit-exact with
+    the oracle.  Fine-size intermediates are materialised -- the fused kernels exist to avoid this."""
+    dco = weighted_block_average(d, w[:, None], f)
+    dup = block_upsample(dco, f)
+    phalf_c = pressure_at_interface(dup, toa_pressure)
+    phalf_f = pressure_at_interface(d, toa_pressure)
+    if mask_mode == "pfull":
+        nb0, km = dup.shape[:2]
+        ncol = dup.shape[-2] * dup.shape[-1]
+        pfull = torch.empty_like(dup)
+        rc = _lib.load().b200cs_pressure_at_midpoint_log(dup.contiguous().data_ptr(), pfull.data_ptr(), _DT[dup.dtype], nb0,
+                                                         km, ncol, float(toa_pressure), _stream())
+        _lib.check(rc, "pressure_at_midpoint_log")
+        masked = mask_weights(w, pfull, phalf_f, "pfull")
+    else:
+        masked = mask_weights(w, phalf_c, phalf_f, mask_mode)
+    outs = []
+    for x in fs:
+        reg = regrid_vertical(phalf_f, x, phalf_c, iv=iv, kord=kord)
+        outs.append(weighted_block_average(reg, masked, f))
     return outs, dco
 
 

@@ -39,6 +39,14 @@ struct PeerOut {
     float* base[8];
 };
 
+// Wide windows (f = 16, 32, 64; b200cs_pressure_coarsen_wide): the coarse delp comes from a
+// block-average pre-pass, every CTA leaves partial sums that a second kernel adds in a fixed order.
+struct WideArgs {
+    int f;
+    const float* delp_c;  // [nb0, km, ny/f, nx/f]
+    float* partial;       // [CTA][km][cells per CTA][NF + 1]
+};
+
 template <int NF>
 struct FieldPtrs {
     const void* in[NF];

@@ -10,6 +10,8 @@ int pc_entry_fx4_m1(const PcArgs&, int, int);
 int pc_entry_fx8_m1(const PcArgs&, int, int);
 bool pc_fast_covers(const PcArgs&, int, int, int);
 int pc_fast_entry(const PcArgs&);
+int64_t pc_wide_workspace_floats(int64_t nb0, int km, int64_t ny, int64_t nx, int f);
+int pc_wide_entry(const PcArgs&, float* ws);
 }  // namespace b200cs
 
 using namespace b200cs;
@@ -100,4 +102,37 @@ extern "C" int b200cs_pressure_coarsen_gather(int nfields, const void* const* fi
     return pc_dispatch(nfields, fields, field_dtype, field_stride, delp, p_dtype, delp_stride, w, w_dtype, w_stride, out,
                        delp_coarse, nb0, km, ny, nx, fy, fx, toa_pressure, mask_mode, iv, kord, mode, npeers, peer_out,
                        workspace, workspace_bytes, stream);
+}
+
+extern "C" int64_t b200cs_pressure_coarsen_wide_workspace_bytes(int64_t nb0, int km, int64_t ny, int64_t nx, int factor) {
+    if (factor < 16 || nb0 < 0 || km < 1 || ny < 1 || nx < 1) return 0;
+    return (int64_t)sizeof(float) * pc_wide_workspace_floats(nb0, km, ny, nx, factor);
+}
+
+extern "C" int b200cs_pressure_coarsen_wide(int nfields, const void* const* fields, const int64_t field_stride[3],
+                                            const void* delp, const int64_t delp_stride[3], const void* w,
+                                            const int64_t w_stride[2], void* const* out, void* delp_coarse,
+                                            int64_t nb0, int km, int64_t ny, int64_t nx, int factor,
+                                            double toa_pressure, int mask_mode, int iv, int kord, void* workspace,
+                                            int64_t workspace_bytes, void* stream) {
+    B200CS_REQUIRE(nfields >= 1 && nfields <= B200CS_MAX_FIELDS, "pressure_coarsen_wide: nfields must be 1..%d", B200CS_MAX_FIELDS);
+    B200CS_REQUIRE(fields && out && field_stride && delp && w && delp_stride && w_stride, "pressure_coarsen_wide: NULL argument");
+    for (int i = 0; i < nfields; i++) B200CS_REQUIRE(fields[i] && out[i], "pressure_coarsen_wide: field %d is NULL", i);
+    B200CS_REQUIRE(factor == 16 || factor == 32 || factor == 64, "pressure_coarsen_wide: factor must be 16, 32 or 64 (got %d)", factor);
+    B200CS_REQUIRE(nb0 >= 0 && nb0 <= 65535 && ny >= 1 && nx >= 1 && ny % factor == 0 && nx % factor == 0,
+                   "pressure_coarsen_wide: extents must be multiples of the window");
+    B200CS_REQUIRE((ny + kTileY - 1) / kTileY <= 65535, "pressure_coarsen_wide: ny too large");
+    B200CS_REQUIRE(km >= 4, "pressure_coarsen_wide: km=%d; the PPM profile needs at least 4 levels", km);
+    B200CS_REQUIRE(mask_mode >= B200CS_MASK_NONE && mask_mode <= B200CS_MASK_PFULL, "pressure_coarsen_wide: bad mask_mode");
+    if (kord > 3) return set_err(B200CS_EUNSUPPORTED, "pressure_coarsen_wide: kord <= 3 only (got %d)", kord);
+    if (nb0 == 0) return B200CS_OK;
+    const int64_t need = b200cs_pressure_coarsen_wide_workspace_bytes(nb0, km, ny, nx, factor);
+    if (!workspace || workspace_bytes < need)
+        return set_err(B200CS_EWORKSPACE, "pressure_coarsen_wide: workspace of %lld bytes needed", (long long)need);
+    PcArgs a{nfields, fields, B200CS_F32, field_stride, delp, delp_stride, w, w_stride, out, delp_coarse,
+             nb0, km, ny, nx, factor, factor, toa_pressure, mask_mode, iv, kord, as_stream(stream), 0};
+    const int64_t span_q = (int64_t)km * field_stride[1] * 4, span_d = (int64_t)km * delp_stride[1] * 4;
+    B200CS_REQUIRE(field_stride[1] >= 0 && delp_stride[1] >= 0 && span_q < (int64_t)0xffffffff && span_d < (int64_t)0xffffffff,
+                   "pressure_coarsen_wide: a column must span less than 4 GiB");
+    return pc_wide_entry(a, (float*)workspace);
 }

@@ -19,4 +19,21 @@ int pc_fast_entry(const PcArgs& a) {
     if (a.fy == 8) return launch_pc_sweep_fields<8>(a);
     return launch_pc_sweep_fields<1>(a);
 }
+// wide windows (f = 16, 32, 64): block-average pre-pass for the coarse delp, sweep kernel with
+// per-CTA partial sums, fixed-order finalize (pressure_coarsen_sweep.cuh)
+int64_t pc_wide_workspace_floats(int64_t nb0, int km, int64_t ny, int64_t nx, int f) {
+    return nb0 * km * (ny / f) * (nx / f) + pc_wide_partial_floats(nb0, km, ny, nx, f);
+}
+int pc_wide_entry(const PcArgs& a, float* ws) {
+    const int f = a.fx;
+    float* delp_c = a.delp_coarse ? (float*)a.delp_coarse : ws;
+    float* partial = ws + a.nb0 * a.km * (a.ny / f) * (a.nx / f);
+    const int64_t ds[3] = {a.dstride[0], a.dstride[1], a.dstride[2]};
+    const int64_t wst[3] = {a.wstride[0], 0, a.wstride[1]};
+    // coarse delp: the streaming wide-window block average of block_ops.cu (numpy order, bit-exact)
+    int rc = b200cs_weighted_block_average(a.delp, B200CS_F32, ds, a.w, B200CS_F32, wst, nullptr, 0, nullptr, delp_c,
+                                           B200CS_F32, a.nb0, a.km, a.ny, a.nx, f, f, f, f, (void*)a.st);
+    if (rc != B200CS_OK) return rc;
+    return launch_pc_sweep_wide_fields(a, delp_c, partial);
+}
 }  // namespace b200cs

@@ -207,13 +207,14 @@ __device__ __forceinline__ void sweep_enter(SweepCtx<NF>& c, int L, int iv) {
 // four of them in one LDS.128)
 __host__ __device__ inline int sweep_lvl_stride(int km) { return ((km + 1 + 6) / 8) * 8 + 1; }
 
-template <int NF, int FY>
+template <int NF, int FY, bool WIDE = false>
 __global__ void __launch_bounds__(kThreads, 2)
 pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_t fsy,
                               const float* __restrict__ delp, int64_t ds0, int64_t dsl, int64_t dsy,
                               const float* __restrict__ w, int64_t ws0, int64_t wsy,
                               float* __restrict__ delp_coarse, int km, int64_t ny, int64_t nx, float toa,
-                              int mask_mode, int iv, int seq_i, const __grid_constant__ PeerOut peers, int first) {
+                              int mask_mode, int iv, int seq_i, const __grid_constant__ PeerOut peers, int first,
+                              const __grid_constant__ WideArgs wide) {
     constexpr int FX = 8;
     const bool seq = seq_i != 0;
     constexpr int CW = kTileX / FX;   // cells per tile row
@@ -228,7 +229,8 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
     const int64_t x = xg < nx ? xg : nx - 1, y = yg < ny ? yg : ny - 1;
     const int64_t cxN = nx / FX, cyN = ny / FY;
     // shadow threads also take the cell of the column they shadow (its levels are defined)
-    const int my_cell = (ty / FY) * CW + (int)(x - (int64_t)blockIdx.x * kTileX) / FX;
+    int my_cell = (ty / FY) * CW + (int)(x - (int64_t)blockIdx.x * kTileX) / FX;
+    if constexpr (WIDE) my_cell = (int)(x - (int64_t)blockIdx.x * kTileX) / (wide.f < kTileX ? wide.f : kTileX);
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float4* s_lvl = reinterpret_cast<float4*>(smem_raw);                    // [NCELL][km+1], last = sentinel
@@ -256,73 +258,90 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
     // ---------------- Phase A: coarse pressure levels of the tile's cells -------------------
     const float wv = active ? __ldg(w + b0 * ws0 + y * wsy + x) : 0.f;
     const float wrow = reduce_row8(nan_to_zero(wv), seq, lane);  // weight sum of this window row
-    if ((lane & (FX - 1)) == 0) s_rows[ty * CW + lane / FX] = wrow;
-    __syncthreads();
-    if (tid < NCELL) {
-        const int cyi = tid / CW, cxi = tid % CW;
-        float d = 0.f;
-        for (int r = 0; r < FY; r++) d = d + s_rows[(cyi * FY + r) * CW + cxi];
-        s_den[tid] = d;
-    }
-    __syncthreads();
-    // Products delp*w go to shared memory level by level (conflict-free: one 128-B line per row);
-    // one thread per (level, cell) then adds its window rows from two LDS.128 each, in numpy's
-    // order and entirely in registers -- no shuffles.  The staging ring of Phase B is not in use
-    // yet and lends its memory.
-    constexpr int kProdLevel = kTileY * kTileX + 4;  // +4 words: levels start 4 banks apart
-    float* s_prod = reinterpret_cast<float*>(s_buf);  // [2][KA][kProdLevel]
-    static_assert(2 * kFastKA * kProdLevel * sizeof(float) <= kStage * kThreads * sizeof(float4), "s_prod must fit in s_buf");
     float pacc = toa;
-    float dn[kFastKA];  // next chunk of delp, in flight while the current one is reduced
-#pragma unroll
-    for (int kk = 0; kk < kFastKA; kk++) dn[kk] = (kk < km) ? __ldg(dcol + (int64_t)kk * dsl) : 0.f;
-    for (int k0 = 0; k0 < km; k0 += kFastKA) {
-        const int buf = (k0 / kFastKA) & 1;
-        float d[kFastKA], pr[kFastKA];
-#pragma unroll
-        for (int kk = 0; kk < kFastKA; kk++) d[kk] = dn[kk];
-#pragma unroll
-        for (int kk = 0; kk < kFastKA; kk++)
-            dn[kk] = (k0 + kFastKA + kk < km) ? __ldg(dcol + (int64_t)(k0 + kFastKA + kk) * dsl) : 0.f;
-        float chk = 0.f;
-#pragma unroll
-        for (int kk = 0; kk < kFastKA; kk++) { pr[kk] = d[kk] * wv; chk += pr[kk]; }
-        if (__any_sync(0xffffffffu, chk != chk)) {  // NaN in delp or weights: rare, exact handling
-#pragma unroll
-            for (int kk = 0; kk < kFastKA; kk++) { d[kk] = nan_to_zero(d[kk]); pr[kk] = nan_to_zero(pr[kk]); }
-        }
-        float* sp = s_prod + (size_t)buf * kFastKA * kProdLevel + tid;
-#pragma unroll
-        for (int kk = 0; kk < kFastKA; kk++) {
-            pacc = pacc + d[kk];  // xarray cumsum == nancumsum (levels beyond km add 0)
-            sp[kk * kProdLevel] = pr[kk];
+    if constexpr (!WIDE) {
+        if ((lane & (FX - 1)) == 0) s_rows[ty * CW + lane / FX] = wrow;
+        __syncthreads();
+        if (tid < NCELL) {
+            const int cyi = tid / CW, cxi = tid % CW;
+            float d = 0.f;
+            for (int r = 0; r < FY; r++) d = d + s_rows[(cyi * FY + r) * CW + cxi];
+            s_den[tid] = d;
         }
         __syncthreads();
-        // KA*NCELL (level, cell) sums per chunk, handed to a different warp each chunk
-        const int t = (tid - (k0 / kFastKA) * 32) & (kThreads - 1);
-        if (t < kFastKA * NCELL) {
-            const int kk = t / NCELL, cc = t % NCELL, k = k0 + kk;
-            if (k < km) {
-                const int cyi = cc / CW, cxi = cc % CW;
-                const float* src = s_prod + (size_t)(buf * kFastKA + kk) * kProdLevel + cxi * FX;
-                float num = 0.f;
-#pragma unroll
-                for (int r = 0; r < FY; r++) {
-                    const float4 a = *reinterpret_cast<const float4*>(src + (cyi * FY + r) * kTileX);
-                    const float4 b = *reinterpret_cast<const float4*>(src + (cyi * FY + r) * kTileX + 4);
-                    float rs;
-                    if (seq) rs = ((((((((0.f + a.x) + a.y) + a.z) + a.w) + b.x) + b.y) + b.z) + b.w);
-                    else rs = ((a.x + a.y) + (a.z + a.w)) + ((b.x + b.y) + (b.z + b.w));
-                    num = num + rs;
-                }
-                const float dc = num / s_den[cc];
-                s_lvl[cc * LS + k].w = dc;
-                const int64_t cyg = (int64_t)blockIdx.y * CH + cyi, cxg = (int64_t)blockIdx.x * CW + cxi;
-                if (delp_coarse && cyg < cyN && cxg < cxN) delp_coarse[((b0 * km + k) * cyN + cyg) * cxN + cxg] = dc;
+        // Products delp*w go to shared memory level by level (conflict-free: one 128-B line per row);
+        // one thread per (level, cell) then adds its window rows from two LDS.128 each, in numpy's
+        // order and entirely in registers -- no shuffles.  The staging ring of Phase B is not in use
+        // yet and lends its memory.
+        constexpr int kProdLevel = kTileY * kTileX + 4;  // +4 words: levels start 4 banks apart
+        float* s_prod = reinterpret_cast<float*>(s_buf);  // [2][KA][kProdLevel]
+        static_assert(2 * kFastKA * kProdLevel * sizeof(float) <= kStage * kThreads * sizeof(float4), "s_prod must fit in s_buf");
+        float dn[kFastKA];  // next chunk of delp, in flight while the current one is reduced
+    #pragma unroll
+        for (int kk = 0; kk < kFastKA; kk++) dn[kk] = (kk < km) ? __ldg(dcol + (int64_t)kk * dsl) : 0.f;
+        for (int k0 = 0; k0 < km; k0 += kFastKA) {
+            const int buf = (k0 / kFastKA) & 1;
+            float d[kFastKA], pr[kFastKA];
+    #pragma unroll
+            for (int kk = 0; kk < kFastKA; kk++) d[kk] = dn[kk];
+    #pragma unroll
+            for (int kk = 0; kk < kFastKA; kk++)
+                dn[kk] = (k0 + kFastKA + kk < km) ? __ldg(dcol + (int64_t)(k0 + kFastKA + kk) * dsl) : 0.f;
+            float chk = 0.f;
+    #pragma unroll
+            for (int kk = 0; kk < kFastKA; kk++) { pr[kk] = d[kk] * wv; chk += pr[kk]; }
+            if (__any_sync(0xffffffffu, chk != chk)) {  // NaN in delp or weights: rare, exact handling
+    #pragma unroll
+                for (int kk = 0; kk < kFastKA; kk++) { d[kk] = nan_to_zero(d[kk]); pr[kk] = nan_to_zero(pr[kk]); }
             }
+            float* sp = s_prod + (size_t)buf * kFastKA * kProdLevel + tid;
+    #pragma unroll
+            for (int kk = 0; kk < kFastKA; kk++) {
+                pacc = pacc + d[kk];  // xarray cumsum == nancumsum (levels beyond km add 0)
+                sp[kk * kProdLevel] = pr[kk];
+            }
+            __syncthreads();
+            // KA*NCELL (level, cell) sums per chunk, handed to a different warp each chunk
+            const int t = (tid - (k0 / kFastKA) * 32) & (kThreads - 1);
+            if (t < kFastKA * NCELL) {
+                const int kk = t / NCELL, cc = t % NCELL, k = k0 + kk;
+                if (k < km) {
+                    const int cyi = cc / CW, cxi = cc % CW;
+                    const float* src = s_prod + (size_t)(buf * kFastKA + kk) * kProdLevel + cxi * FX;
+                    float num = 0.f;
+    #pragma unroll
+                    for (int r = 0; r < FY; r++) {
+                        const float4 a = *reinterpret_cast<const float4*>(src + (cyi * FY + r) * kTileX);
+                        const float4 b = *reinterpret_cast<const float4*>(src + (cyi * FY + r) * kTileX + 4);
+                        float rs;
+                        if (seq) rs = ((((((((0.f + a.x) + a.y) + a.z) + a.w) + b.x) + b.y) + b.z) + b.w);
+                        else rs = ((a.x + a.y) + (a.z + a.w)) + ((b.x + b.y) + (b.z + b.w));
+                        num = num + rs;
+                    }
+                    const float dc = num / s_den[cc];
+                    s_lvl[cc * LS + k].w = dc;
+                    const int64_t cyg = (int64_t)blockIdx.y * CH + cyi, cxg = (int64_t)blockIdx.x * CW + cxi;
+                    if (delp_coarse && cyg < cyN && cxg < cxN) delp_coarse[((b0 * km + k) * cyN + cyg) * cxN + cxg] = dc;
+                }
+            }
+            // s_prod is double-buffered: the barrier of the next chunk orders these reads before the
+            // chunk after that overwrites this half
         }
-        // s_prod is double-buffered: the barrier of the next chunk orders these reads before the
-        // chunk after that overwrites this half
+    } else {
+        // coarse delp of the tile's cell(s) from the block-average pre-pass; the fine surface
+        // pressure is the sequential cumsum of the column (the mask compares against it)
+        const int ncx = wide.f < kTileX ? kTileX / wide.f : 1;
+        const int64_t cyW = ny / wide.f, cxW = nx / wide.f;
+        const int64_t cyg = ((int64_t)blockIdx.y * kTileY) / wide.f;
+        for (int t = tid; t < ncx * km; t += kThreads) {
+            const int cc = t / km, k = t % km;
+            const int64_t cxg = ((int64_t)blockIdx.x * kTileX) / wide.f + cc;
+            float dc = 0.f;
+            if (cyg < cyW && cxg < cxW) dc = __ldg(wide.delp_c + ((b0 * km + k) * cyW + cyg) * cxW + cxg);
+            s_lvl[cc * LS + k].w = dc;
+        }
+#pragma unroll 8
+        for (int k = 0; k < km; k++) pacc = pacc + nan_to_zero(__ldg(dcol + (int64_t)k * dsl));
     }
     __syncthreads();
     // coarse interfaces: the cumsum is sequential (exact) and touches nothing else; meanwhile the
@@ -418,24 +437,39 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
     __syncthreads();
 
     // ---------------- Phase C: rows in row order, divide, store ------------------------------
-    for (int t = tid; t < km * NCELL; t += kThreads) {
-        const int cc = t % NCELL, k = t / NCELL;
-        const int cyi = cc / CW, cxi = cc % CW;
-        const int64_t cyg = (int64_t)blockIdx.y * CH + cyi, cxg = (int64_t)blockIdx.x * CW + cxi;
-        if (cyg < cyN && cxg < cxN) {
-            float num[NF], den = 0.f;
-#pragma unroll
-            for (int i = 0; i < NF; i++) num[i] = 0.f;
-#pragma unroll
-            for (int r = 0; r < FY; r++) {
-                const float* src = s_acc + ((size_t)((cyi * FY + r) * km + k) * CW + cxi) * NV;
-#pragma unroll
-                for (int i = 0; i < NF; i++) num[i] = num[i] + src[i];
-                den = den + src[NF];
+    if constexpr (!WIDE) {
+        for (int t = tid; t < km * NCELL; t += kThreads) {
+            const int cc = t % NCELL, k = t / NCELL;
+            const int cyi = cc / CW, cxi = cc % CW;
+            const int64_t cyg = (int64_t)blockIdx.y * CH + cyi, cxg = (int64_t)blockIdx.x * CW + cxi;
+            if (cyg < cyN && cxg < cxN) {
+                float num[NF], den = 0.f;
+    #pragma unroll
+                for (int i = 0; i < NF; i++) num[i] = 0.f;
+    #pragma unroll
+                for (int r = 0; r < FY; r++) {
+                    const float* src = s_acc + ((size_t)((cyi * FY + r) * km + k) * CW + cxi) * NV;
+    #pragma unroll
+                    for (int i = 0; i < NF; i++) num[i] = num[i] + src[i];
+                    den = den + src[NF];
+                }
+                const int64_t o = ((b0 * km + k) * cyN + cyg) * cxN + cxg;
+    #pragma unroll
+                for (int i = 0; i < NF; i++) ((float*)fp.out[i])[o] = num[i] / den;
             }
-            const int64_t o = ((b0 * km + k) * cyN + cyg) * cxN + cxg;
-#pragma unroll
-            for (int i = 0; i < NF; i++) ((float*)fp.out[i])[o] = num[i] / den;
+        }
+    } else {
+        // partial sums of this CTA per (level, cell of the tile): rows, then the 8-lane groups of
+        // the cell, in a fixed order; wide_finalize_kernel adds the CTAs of a cell and divides
+        const int ncx = wide.f < kTileX ? kTileX / wide.f : 1;
+        const int gpc = CW / ncx;
+        const int64_t cta = ((int64_t)b0 * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        for (int t = tid; t < km * ncx * NV; t += kThreads) {
+            const int v = t % NV, cc = (t / NV) % ncx, k = t / (NV * ncx);
+            float sum = 0.f;
+            for (int r = 0; r < kTileY; r++)
+                for (int g = 0; g < gpc; g++) sum = sum + s_acc[((size_t)(r * km + k) * CW + cc * gpc + g) * NV + v];
+            wide.partial[((cta * km + k) * ncx + cc) * NV + v] = sum;
         }
     }
 
@@ -517,7 +551,7 @@ int launch_pc_sweep(const PcArgs& a, int first) {
     kern<<<grid, kThreads, smem, a.st>>>(fp, a.fstride[0], a.fstride[1], a.fstride[2], (const float*)a.delp,
                                          a.dstride[0], a.dstride[1], a.dstride[2], (const float*)a.w, a.wstride[0],
                                          a.wstride[1], first == 0 ? (float*)a.delp_coarse : nullptr, a.km, a.ny, a.nx,
-                                         (float)a.toa, a.mask_mode, a.iv, a.seq, po, first);
+                                         (float)a.toa, a.mask_mode, a.iv, a.seq, po, first, WideArgs{});
     return check_launch("pressure_coarsen(fast)");
 }
 
@@ -530,6 +564,75 @@ int launch_pc_sweep_fields(const PcArgs& a) {
         if (left >= 4) { rc = launch_pc_sweep<4, FY>(a, first); first += 4; }
         else if (left >= 2) { rc = launch_pc_sweep<2, FY>(a, first); first += 2; }
         else { rc = launch_pc_sweep<1, FY>(a, first); first += 1; }
+        if (rc != B200CS_OK) return rc;
+    }
+    return B200CS_OK;
+}
+
+// ---- wide windows (f = 16, 32, 64) -----------------------------------------------------------
+
+template <int NF>
+__global__ void wide_finalize_kernel(const float* __restrict__ partial, FieldPtrs<NF> fp, int64_t nb0, int km,
+                                     int64_t cyW, int64_t cxW, int f, int gx, int gy) {
+    constexpr int NV = NF + 1;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nb0 * km * cyW * cxW) return;
+    const int64_t cxg = t % cxW, cyg = (t / cxW) % cyW, k = (t / (cxW * cyW)) % km, b0 = t / (cxW * cyW * km);
+    const int ncx = f < kTileX ? kTileX / f : 1, ntx = f < kTileX ? 1 : f / kTileX, nty = f / kTileY;
+    const int64_t bx0 = f < kTileX ? cxg / ncx : cxg * ntx, by0 = cyg * nty;
+    const int cxl = f < kTileX ? (int)(cxg % ncx) : 0;
+    float num[NF], den = 0.f;
+#pragma unroll
+    for (int i = 0; i < NF; i++) num[i] = 0.f;
+    for (int ry = 0; ry < nty; ry++)
+        for (int rx = 0; rx < ntx; rx++) {
+            const int64_t cta = (b0 * gy + by0 + ry) * gx + bx0 + rx;
+            const float* p = partial + ((cta * km + k) * ncx + cxl) * NV;
+#pragma unroll
+            for (int i = 0; i < NF; i++) num[i] = num[i] + p[i];
+            den = den + p[NF];
+        }
+#pragma unroll
+    for (int i = 0; i < NF; i++) ((float*)fp.out[i])[t] = num[i] / den;
+}
+
+inline int64_t pc_wide_partial_floats(int64_t nb0, int km, int64_t ny, int64_t nx, int f) {
+    const int64_t gx = (nx + kTileX - 1) / kTileX, gy = (ny + kTileY - 1) / kTileY;
+    return nb0 * gy * gx * km * (f < kTileX ? kTileX / f : 1) * 5;  // NV <= 5
+}
+
+template <int NF>
+int launch_pc_sweep_wide(const PcArgs& a, int first, const float* delp_c, float* partial) {
+    auto kern = pressure_coarsen_sweep_kernel<NF, 8, true>;
+    const size_t smem = pressure_coarsen_sweep_smem<NF, 8>(a.km);
+    if (smem > 227 * 1024)
+        return set_err(B200CS_EUNSUPPORTED, "pressure_coarsen(wide): km=%d needs %zu B of shared memory (> 227 KB)", a.km, smem);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return set_err(B200CS_ECUDA, "pressure_coarsen(wide): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    FieldPtrs<NF> fp;
+    for (int i = 0; i < NF; i++) { fp.in[i] = a.fields[first + i]; fp.out[i] = a.out[first + i]; }
+    dim3 grid((unsigned)((a.nx + kTileX - 1) / kTileX), (unsigned)((a.ny + kTileY - 1) / kTileY), (unsigned)a.nb0);
+    WideArgs wa{a.fx, delp_c, partial};
+    kern<<<grid, kThreads, smem, a.st>>>(fp, a.fstride[0], a.fstride[1], a.fstride[2], (const float*)a.delp,
+                                         a.dstride[0], a.dstride[1], a.dstride[2], (const float*)a.w, a.wstride[0],
+                                         a.wstride[1], nullptr, a.km, a.ny, a.nx, (float)a.toa, a.mask_mode, a.iv, 0,
+                                         PeerOut{}, first, wa);
+    int rc = check_launch("pressure_coarsen(wide)");
+    if (rc != B200CS_OK) return rc;
+    const int64_t cyW = a.ny / a.fx, cxW = a.nx / a.fx, n = a.nb0 * a.km * cyW * cxW;
+    wide_finalize_kernel<NF><<<(unsigned)((n + 255) / 256), 256, 0, a.st>>>(partial, fp, a.nb0, a.km, cyW, cxW, a.fx,
+                                                                           (int)grid.x, (int)grid.y);
+    return check_launch("pressure_coarsen(wide finalize)");
+}
+
+inline int launch_pc_sweep_wide_fields(const PcArgs& a, const float* delp_c, float* partial) {
+    int first = 0;
+    while (first < a.nfields) {
+        const int left = a.nfields - first;
+        int rc;
+        if (left >= 4) { rc = launch_pc_sweep_wide<4>(a, first, delp_c, partial); first += 4; }
+        else if (left >= 2) { rc = launch_pc_sweep_wide<2>(a, first, delp_c, partial); first += 2; }
+        else { rc = launch_pc_sweep_wide<1>(a, first, delp_c, partial); first += 1; }
         if (rc != B200CS_OK) return rc;
     }
     return B200CS_OK;

@@ -226,6 +226,25 @@ int b200cs_pressure_coarsen_gather(int nfields, const void* const* fields, int f
                                    int64_t workspace_bytes, void* stream);
 
 /*
+ * Wide windows: the fused pressure-level coarse-graining for factor 16, 32 or 64 (C3072 -> C48 is
+ * factor 64).  fp32 data, FAST arithmetic, kord <= 3, square windows.  A coarse cell now spans
+ * several CTAs: (1) b200cs_weighted_block_average forms the coarse delp (numpy order, bit-exact),
+ * (2) the sweep kernel remaps / masks / weights every fine column against it and leaves per-CTA
+ * partial sums, (3) a finalize kernel adds the partial sums of a cell in a fixed order and divides.
+ * Deterministic (no atomics); values within 1e-6 of the unfused EXACT operators.  Arguments as
+ * b200cs_pressure_coarsen; delp_coarse may be NULL.
+ */
+int64_t b200cs_pressure_coarsen_wide_workspace_bytes(int64_t nb0, int km, int64_t ny, int64_t nx,
+                                                     int factor);
+int b200cs_pressure_coarsen_wide(int nfields, const void* const* fields,
+                                 const int64_t field_stride[3], const void* delp,
+                                 const int64_t delp_stride[3], const void* w,
+                                 const int64_t w_stride[2], void* const* out, void* delp_coarse,
+                                 int64_t nb0, int km, int64_t ny, int64_t nx, int factor,
+                                 double toa_pressure, int mask_mode, int iv, int kord,
+                                 void* workspace, int64_t workspace_bytes, void* stream);
+
+/*
  * Below-surface weight mask for the unfused path and API parity with _mask_weights
  * (VCM/cubedsphere/regridz.py:200-220): out[b,k,col] = cond ? w[b,col] : 0 with
  *   PHALF: phalf_coarse_on_fine[b,k+1,col] < phalf_fine[b,km,col]

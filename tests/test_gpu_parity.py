@@ -763,3 +763,32 @@ def test_fused_gather_slots_single_gpu(core):
     from fv3net_b200._lib import B200csError
     with pytest.raises(B200csError, match="only the FAST"):
         core.pressure_coarsen(fields, delp, area, f, mode=core.EXACT, peer_ptrs=[slots[0].data_ptr()])
+
+
+# ------------------------------------------------------------------------------------------
+# wide windows (factor 16 / 32 / 64; BASELINE configs[4]: C3072 -> C48 is factor 64)
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("f,n", [(16, 64), (32, 64), (64, 128), (16, 96)])
+@pytest.mark.parametrize("mask_mode", ["phalf", "pfull", "none"])
+def test_pressure_coarsen_wide(core, oracle, f, n, mask_mode):
+    rng = np.random.default_rng(71 + f)
+    nb, km = 2, 14
+    delp = _synthetic_columns(rng, nb, km, n, np.float32)
+    area = rng.uniform(0.5, 1, size=(nb, n, n)).astype(np.float32)
+    fields = [rng.uniform(180, 320, size=(nb, km, n, n)).astype(np.float32)] + \
+             [rng.normal(0, 10, size=(nb, km, n, n)).astype(np.float32) for _ in range(4)]  # 4 + 1 launches
+    fields[1][0, 3, 5, 7] = np.nan
+    exact, edc = core.pressure_coarsen(fields, delp, area, f, 300.0, mask_mode=mask_mode, mode=core.EXACT)  # unfused operators
+    fast, fdc = core.pressure_coarsen(fields, delp, area, f, 300.0, mask_mode=mask_mode, mode=core.FAST)    # wide fused kernel
+    assert eq(edc, fdc)  # coarse delp: the same block-average kernel
+    for e, g, scale in zip(exact, fast, [320.0, 30.0, 30.0, 30.0, 30.0]):
+        assert e.shape == g.shape == (nb, km, n // f, n // f)
+        assert np.array_equal(np.isnan(e), np.isnan(g))
+        assert np.nanmax(np.abs(e - g)) <= 1e-6 * scale
+    # the unfused EXACT chain is the reference's chain: bit-exact with the oracle
+    if mask_mode != "none":
+        reg, masked = oracle.regrid_to_area_weighted_pressure({"a": fields[0]}, delp, area[:, None], 300.0, f,
+                                                              extrapolate=(mask_mode == "pfull"))
+        assert eq(exact[0], oracle.weighted_block_average(reg["a"], masked, f))
+    again, _ = core.pressure_coarsen(fields, delp, area, f, 300.0, mask_mode=mask_mode, mode=core.FAST)
+    assert all(eq(a, b) for a, b in zip(fast, again))  # deterministic: fixed-order partial sums, no atomics
