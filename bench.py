@@ -193,6 +193,120 @@ def run_reference(args):
     }))
 
 
+def run_c3072(args):
+    """BASELINE configs[4] / SURVEY.md 8d config 5: one C3072 -> C48 timestep (factor 64), delp + 4
+    fields, fp32, 6 tiles x 79 levels x 3072 x 3072 = 89.7 GB of input, sharded by (tile, coarse
+    row) over the ranks with no data-path collective (fv3net_b200/shard.py); an asynchronous NCCL
+    all_gather collects the coarse outputs (21.8 MB in total).  Strong scaling: the work is fixed."""
+    import torch
+    import torch.distributed as dist
+
+    from fv3net_b200 import core, shard
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n, f, km, nf = 3072, 64, KM, NFIELDS
+    ncy = n // f
+    ranges = shard.plan(NTILE, ncy, world)
+    per = max(hi - lo for lo, hi in ranges)
+    segs = shard.segments(*ranges[rank], ncy)
+    g = torch.Generator(device=dev).manual_seed(3000 + rank)
+    b = torch.diff(torch.linspace(0, 1, km + 1, device=dev) ** 1.6)
+    data = []
+    for tile, cy0, cy1 in segs:  # this rank's row slabs only: [1, km, rows, n]
+        rows = (cy1 - cy0) * f
+        yy = torch.linspace(0, 6, n, device=dev)[cy0 * f:cy1 * f, None]
+        xx = torch.linspace(0, 6, n, device=dev)[None, :]
+        ps = (8.6e4 + 1.4e4 * torch.sin(yy * 1.3 + tile) * torch.cos(xx * 1.1)
+              + 1500 * torch.randn((1, rows, n), device=dev, generator=g)).clamp(5.0e4, 1.04e5)
+        delp = torch.empty((1, km, rows, n), dtype=torch.float32, device=dev)
+        for k in range(km):  # level by level: no 3 GB temporaries
+            delp[:, k] = (ps - TOA) * b[k] * (1 + 0.04 * (torch.rand((1, rows, n), device=dev, generator=g) - 0.5))
+        area = (3.6e8 + 4.7e8 * torch.rand((1, rows, n), device=dev, generator=g)) * (384.0 / n) ** 2
+        fields = [torch.empty((1, km, rows, n), dtype=torch.float32, device=dev) for _ in range(nf)]
+        fields[0].uniform_(180, 320, generator=g)
+        for x in fields[1:]:
+            x.normal_(0, 10, generator=g)
+        data.append((delp, area, fields))
+    mine = torch.zeros((per, nf + 1, km, n // f), dtype=torch.float32, device=dev)
+    gathered = torch.empty((world * per,) + tuple(mine.shape[1:]), dtype=torch.float32, device=dev) if world > 1 else None
+    pending = [None]
+
+    def step():
+        if pending[0] is not None:
+            pending[0].wait()
+        row = 0
+        for delp, area, fields in data:
+            outs, dco = core.pressure_coarsen(fields, delp, area, f, TOA, mask_mode="phalf", mode=core.FAST)
+            t = torch.stack(list(outs) + [dco])[:, 0].permute(2, 0, 1, 3)  # [rows_c, nf+1, km, cx]
+            mine[row:row + t.shape[0]] = t
+            row += t.shape[0]
+        if world > 1:
+            pending[0] = dist.all_gather_into_tensor(gathered, mine, async_op=True)
+
+    def drain():
+        if pending[0] is not None:
+            pending[0].wait()
+            pending[0] = None
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    drain()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
+    steps = min(args.steps, 10)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(steps):
+        step()
+    drain()
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        dist.barrier()
+    ms_per_step = ms / steps
+    points = NTILE * km * n * n * nf
+    alg = algorithmic_bytes(NTILE, km, n, f, nf)
+    peak, peak_src = measured_peak()
+    if rank == 0:
+        print(json.dumps({
+            "metric": "fine grid pts/s, C3072->C48 pressure-level coarsening (delp + 4 fields, 6 tiles x 79 levels)",
+            "value": points / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "C3072->C48 (factor 64) pressure-level coarsening, delp + 4 fields, 89.7 GB, "
+                                   "sharded by (tile, coarse row); wide-window fused kernel (FAST arithmetic)",
+                       "l2": "inputs larger than L2, no flush needed",
+                       "collective": "none" if world == 1 else "NCCL all_gather of the coarse outputs, asynchronous"},
+            "clocks": clocks, "e2e": None, "gpu_launches": steps * len(data) * 3,
+            "roofline": {"bound": "hbm", "achieved": alg / (ms_per_step * 1e-3) / 1e9 / world, "peak": peak, "unit": "GB/s",
+                         "frac": alg / (ms_per_step * 1e-3) / 1e9 / world / peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "wba_wide_f32_kernel<64> + pressure_coarsen_sweep_kernel<4,8,WIDE> + wide_finalize_kernel",
+                         "algorithmic_bytes_per_launch": alg, "note": "per-GPU average over the three kernels of a step"},
+            "cpu_baseline": None}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -202,6 +316,10 @@ def main():
     ap.add_argument("--mode", default="fast", choices=["exact", "fast"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--workload", default="c384", choices=["c384", "c3072"],
+                    help="c384 (default): BASELINE.json's metric, one C384 timestep per GPU (weak scaling); "
+                         "c3072: BASELINE configs[4], ONE C3072 -> C48 timestep (factor 64, delp + 4 fields, 89.7 GB) "
+                         "sharded by (tile, coarse row) over the GPUs (strong scaling)")
     ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
                     help="N>1: 'peer' = the coarsening kernel stores its coarse outputs into every rank's gather "
                          "buffer over NVLink peer memory (fused all-gather); 'nccl' = asynchronous NCCL all_gather")
@@ -210,6 +328,9 @@ def main():
 
     if args.impl == "reference":
         run_reference(args)
+        return
+    if args.workload == "c3072":
+        run_c3072(args)
         return
 
     import torch
