@@ -294,16 +294,19 @@ block_reduce_kernel(const T* __restrict__ obj, int64_t s0, int64_t sy, T* __rest
 // ---------------------------------------------------------------------------------------
 // K4 block upsample (repeat); 4- or 8-byte elements.
 // ---------------------------------------------------------------------------------------
+// One CTA per output row: the row decomposition (64-bit division) happens once per CTA, the
+// coarse row is read once (cx values), the fine row is written with full-width coalesced stores.
 template <typename T>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
 upsample_kernel(const T* __restrict__ in, T* __restrict__ out, int64_t nb, int64_t cy, int64_t cx,
                 int64_t ny, int64_t nx, int fy, int fx) {
-    const int64_t total = nb * ny * nx;
-    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
-         idx += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t x = idx % nx, y = (idx / nx) % ny, b = idx / (nx * ny);
+    const int64_t rows = nb * ny;
+    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+        const int64_t b = row / ny, y = row - b * ny;
         // a staggered axis has (c-1)*f+1 points: index/f maps the last point onto c-1
-        out[idx] = in[(b * cy + y / fy) * cx + x / fx];
+        const T* src = in + (b * cy + y / fy) * cx;
+        T* dst = out + row * nx;
+        for (int x = threadIdx.x; x < (int)nx; x += blockDim.x) dst[x] = __ldg(src + x / fx);
     }
 }
 
@@ -345,18 +348,19 @@ pressure_interface_kernel(const T* __restrict__ delp, int64_t s0, int64_t sl, T*
     }
 }
 
+// grid = (column chunks, level, batch): no per-element index arithmetic, coalesced along columns
 template <typename TW, typename TP>
 __global__ void __launch_bounds__(256)
 mask_weights_kernel(const TW* __restrict__ w, const TP* __restrict__ pc, const TP* __restrict__ pf,
                     TW* __restrict__ out, int64_t nb0, int64_t km, int64_t ncol, int mode) {
-    const int64_t total = nb0 * km * ncol;
-    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
-         idx += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t c = idx % ncol, k = (idx / ncol) % km, b = idx / (ncol * km);
-        const TP surf = pf[(b * (km + 1) + km) * ncol + c];
-        const TP p = (mode == B200CS_MASK_PHALF) ? pc[(b * (km + 1) + k + 1) * ncol + c]
-                                                 : pc[(b * km + k) * ncol + c];
-        out[idx] = (mode == B200CS_MASK_NONE || p < surf) ? w[b * ncol + c] : TW(0);
+    const int64_t k = blockIdx.y;
+    for (int64_t b = blockIdx.z; b < nb0; b += gridDim.z) {
+        const TP* surf = pf + (b * (km + 1) + km) * ncol;
+        const TP* p = (mode == B200CS_MASK_PHALF) ? pc + (b * (km + 1) + k + 1) * ncol : pc + (b * km + k) * ncol;
+        const TW* wb = w + b * ncol;
+        TW* o = out + (b * km + k) * ncol;
+        for (int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; c < ncol; c += (int64_t)gridDim.x * blockDim.x)
+            o[c] = (mode == B200CS_MASK_NONE || p[c] < surf[c]) ? wb[c] : TW(0);
     }
 }
 
@@ -477,9 +481,9 @@ extern "C" int b200cs_block_upsample(const void* in, void* out, int elem_size, i
     if (total == 0) return B200CS_OK;
     cudaStream_t st = as_stream(stream);
     if (elem_size == 4)
-        upsample_kernel<uint32_t><<<grid_for(total, 256), 256, 0, st>>>((const uint32_t*)in, (uint32_t*)out, nb, cy, cx, ny, nx, fy, fx);
+        upsample_kernel<uint32_t><<<(unsigned)(nb * ny < (1 << 30) ? nb * ny : (1 << 30)), 128, 0, st>>>((const uint32_t*)in, (uint32_t*)out, nb, cy, cx, ny, nx, fy, fx);
     else
-        upsample_kernel<uint64_t><<<grid_for(total, 256), 256, 0, st>>>((const uint64_t*)in, (uint64_t*)out, nb, cy, cx, ny, nx, fy, fx);
+        upsample_kernel<uint64_t><<<(unsigned)(nb * ny < (1 << 30) ? nb * ny : (1 << 30)), 128, 0, st>>>((const uint64_t*)in, (uint64_t*)out, nb, cy, cx, ny, nx, fy, fx);
     return check_launch("block_upsample");
 }
 
@@ -526,7 +530,8 @@ extern "C" int b200cs_mask_weights(const void* w, int w_dtype, const void* pc, c
     const int64_t total = nb0 * km * ncol;
     if (total == 0) return B200CS_OK;
     cudaStream_t st = as_stream(stream);
-    const unsigned g = grid_for(total, 256);
+    B200CS_REQUIRE(km <= 65535, "mask_weights: km > 65535");
+    const dim3 g((unsigned)((ncol + 255) / 256 < 65535 ? (ncol + 255) / 256 : 65535), (unsigned)km, (unsigned)(nb0 < 65535 ? nb0 : 65535));
     if (w_dtype == B200CS_F32 && p_dtype == B200CS_F32)
         mask_weights_kernel<float, float><<<g, 256, 0, st>>>((const float*)w, (const float*)pc, (const float*)pf, (float*)out, nb0, km, ncol, mode);
     else if (w_dtype == B200CS_F32 && p_dtype == B200CS_F64)

@@ -47,29 +47,57 @@ __device__ __forceinline__ T ext_at(const T* in, int64_t nb1, int64_t n, int t, 
     return (ax == 0) ? base[ii * n + jj] : base[jj * n + ii];
 }
 
+// One CTA per output line (line-major outputs) or per output row (the full x-stagger): the line
+// decomposition happens once per CTA; interior lines are two coalesced row reads (or two column
+// reads for x lines), only lines 0 and n go through the face-connection table.
 template <typename T>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
 stagger_kernel(const T* __restrict__ in, T* __restrict__ out, int64_t nb1, int64_t n, int axis, int step) {
     // axis: 0 = y (lines are rows), 1 = x (lines are columns)
     const int axis_xy = (axis == 0) ? 1 : 0;
     const int64_t nlines = n / step + 1;
-    const int64_t total = 6 * nb1 * nlines * n;
-    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
-         idx += (int64_t)gridDim.x * blockDim.x) {
-        int64_t i, l;
-        if (axis == 0 || step > 1) {  // line-major output [.., nlines, n]
-            i = idx % n;
-            l = (idx / n) % nlines;
-        } else {  // full x-stagger keeps the natural [.., n, n+1] layout
-            l = idx % nlines;
-            i = (idx / nlines) % n;
+    if (axis == 0 || step > 1) {  // line-major output [6, nb1, nlines, n]
+        const int64_t total = 6 * nb1 * nlines;
+        for (int64_t line = blockIdx.x; line < total; line += gridDim.x) {
+            const int64_t l = line % nlines, b1 = (line / nlines) % nb1;
+            const int t = (int)(line / (nlines * nb1));
+            const int64_t j = l * step;
+            T* dst = out + line * n;
+            if (j > 0 && j < n) {
+                const T* base = in + ((int64_t)t * nb1 + b1) * n * n;
+                if (axis == 0) {
+                    const T* r0 = base + (j - 1) * n;
+                    const T* r1 = base + j * n;
+                    for (int i = threadIdx.x; i < (int)n; i += blockDim.x) dst[i] = T(0.5) * (__ldg(r0 + i) + __ldg(r1 + i));
+                } else {
+                    for (int i = threadIdx.x; i < (int)n; i += blockDim.x)
+                        dst[i] = T(0.5) * (__ldg(base + (int64_t)i * n + j - 1) + __ldg(base + (int64_t)i * n + j));
+                }
+            } else {
+                for (int i = threadIdx.x; i < (int)n; i += blockDim.x)
+                    dst[i] = T(0.5) * (ext_at(in, nb1, n, t, b1, axis_xy, j - 1, (int64_t)i) +
+                                       ext_at(in, nb1, n, t, b1, axis_xy, j, (int64_t)i));
+            }
         }
-        const int64_t b1 = (idx / (n * nlines)) % nb1;
-        const int t = (int)(idx / (n * nlines * nb1));
-        const int64_t j = l * step;
-        const T a = ext_at(in, nb1, n, t, b1, axis_xy, j - 1, i);
-        const T b = ext_at(in, nb1, n, t, b1, axis_xy, j, i);
-        out[idx] = T(0.5) * (a + b);
+    } else {  // full x-stagger keeps the natural [6, nb1, n, n+1] layout: one CTA per row
+        const int64_t total = 6 * nb1 * n;
+        for (int64_t row = blockIdx.x; row < total; row += gridDim.x) {
+            const int64_t y = row % n, b1 = (row / n) % nb1;
+            const int t = (int)(row / (n * nb1));
+            const T* src = in + (((int64_t)t * nb1 + b1) * n + y) * n;
+            T* dst = out + row * (n + 1);
+            for (int jx = threadIdx.x; jx <= (int)n; jx += blockDim.x) {
+                T a, b;
+                if (jx > 0 && jx < (int)n) {
+                    a = __ldg(src + jx - 1);
+                    b = __ldg(src + jx);
+                } else {
+                    a = ext_at(in, nb1, n, t, b1, axis_xy, (int64_t)jx - 1, y);
+                    b = ext_at(in, nb1, n, t, b1, axis_xy, (int64_t)jx, y);
+                }
+                dst[jx] = T(0.5) * (a + b);
+            }
+        }
     }
 }
 
@@ -85,12 +113,12 @@ extern "C" int b200cs_stagger(const void* in, void* out, int dtype, int64_t nb1,
     B200CS_REQUIRE(dtype == B200CS_F32 || dtype == B200CS_F64, "stagger: dtype must be F32 or F64");
     const int64_t total = 6 * nb1 * (n / line_step + 1) * n;
     if (total == 0) return B200CS_OK;
-    int64_t blocks = (total + 255) / 256;
-    if (blocks > 148LL * 32) blocks = 148LL * 32;
+    int64_t blocks = (axis == 0 || line_step > 1) ? 6 * nb1 * (n / line_step + 1) : 6 * nb1 * n;
+    if (blocks > (1LL << 30)) blocks = 1LL << 30;
     cudaStream_t st = as_stream(stream);
     if (dtype == B200CS_F32)
-        stagger_kernel<float><<<(unsigned)blocks, 256, 0, st>>>((const float*)in, (float*)out, nb1, n, axis, line_step);
+        stagger_kernel<float><<<(unsigned)blocks, 128, 0, st>>>((const float*)in, (float*)out, nb1, n, axis, line_step);
     else
-        stagger_kernel<double><<<(unsigned)blocks, 256, 0, st>>>((const double*)in, (double*)out, nb1, n, axis, line_step);
+        stagger_kernel<double><<<(unsigned)blocks, 128, 0, st>>>((const double*)in, (double*)out, nb1, n, axis, line_step);
     return check_launch("stagger");
 }
