@@ -6,6 +6,8 @@
 // All are HBM-bound streaming kernels: 128-bit coalesced loads, every fine byte read once,
 // numerator / denominator / divide fused in one pass.  Compiled with -fmad=false so that
 // x*w is rounded before it is summed, exactly like numpy's materialised `obj * weights`.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b200cs {
@@ -403,7 +405,9 @@ extern "C" int b200cs_weighted_block_average(const void* obj, int obj_dtype, con
         (!w2 || (aligned16(w2) && s4(sv))) && nb0 * nb1 * cy * cx > 0) {
         const int64_t ncell = nb0 * cy * cx;
         const bool w3d = sw[1] != 0;
-        constexpr int LV = 4;
+        // levels per thread: 1 keeps the grid at several waves at C384 (13,824 cells x 79 levels); the
+        // 2-D weights are re-read from L2
+        static const int lv_env = [] { const char* e = getenv("B200CS_WBA_LV"); return e ? atoi(e) : 1; }();
         dim3 grid((unsigned)((ncell + 127) / 128), 1, 1);
 #define B200CS_WBA8(LVV, W3, H2)                                                                     \
     grid.y = (unsigned)((nb1 + LVV - 1) / LVV);                                                      \
@@ -414,7 +418,9 @@ extern "C" int b200cs_weighted_block_average(const void* obj, int obj_dtype, con
                                                        nb0, nb1, cy, cx)
         if (w2) { if (w3d) { B200CS_WBA8(2, true, true); } else { B200CS_WBA8(2, false, true); } }
         else if (w3d) { B200CS_WBA8(2, true, false); }
-        else { B200CS_WBA8(LV, false, false); }
+        else if (lv_env == 4) { B200CS_WBA8(4, false, false); }
+        else if (lv_env == 2) { B200CS_WBA8(2, false, false); }
+        else { B200CS_WBA8(1, false, false); }
 #undef B200CS_WBA8
         return check_launch("weighted_block_average(8x8 f32)");
     }
