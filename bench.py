@@ -193,6 +193,24 @@ def run_reference(args):
     }))
 
 
+def bind_to_gpu_numa_node(index):
+    """Pins this process to the CPUs NVML reports as local to its GPU, so that the pinned host
+    buffers of the end-to-end leg are first-touched on that NUMA node (with 8 ranks on one box the
+    uploads otherwise all pull from one node's memory)."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = [64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1]
+        cpus = [c for c in cpus if c in os.sched_getaffinity(0)]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:
+        pass
+
+
 def run_c3072(args):
     """BASELINE configs[4] / SURVEY.md 8d config 5: one C3072 -> C48 timestep (factor 64), delp + 4
     fields, fp32, 6 tiles x 79 levels x 3072 x 3072 = 89.7 GB of input, sharded by (tile, coarse
@@ -343,6 +361,7 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    bind_to_gpu_numa_node(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     mode = core.EXACT if args.mode == "exact" else core.FAST
@@ -361,9 +380,17 @@ def main():
         # symmetric-memory buffer while it computes; a device-side barrier per step orders readers
         from fv3net_b200.gather import CoarseGather
 
-        gath = [CoarseGather(NFIELDS, NTILE, KM, cdim, cdim, dev) for _ in range(nbuf)]
+        try:
+            gath = [CoarseGather(NFIELDS, NTILE, KM, cdim, cdim, dev) for _ in range(nbuf)]
+            ok = 1
+        except Exception as e:  # no peer mapping on this box: every rank falls back to the NCCL gather
+            print(f"[bench] rank {rank}: symmetric memory unavailable ({e}); using --collective nccl", file=sys.stderr)
+            ok = 0
+        flag = torch.tensor([ok], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        use_peer = bool(flag.item())
         local = torch.empty((NFIELDS + 1, NTILE, KM, cdim, cdim), dtype=torch.float32, device=dev)
-    else:
+    if not use_peer:
         mine = [torch.empty((NFIELDS + 1, NTILE, KM, cdim, cdim), dtype=torch.float32, device=dev) for _ in range(nbuf)]
         gathered = [torch.empty((world,) + tuple(mine[0].shape), dtype=torch.float32, device=dev) for _ in range(nbuf)] if world > 1 else None
 
