@@ -168,9 +168,10 @@ def block_reduce(obj, coarsening_factor, method="sum", skipna=True, edge=None, p
     return _ret(out, was_np)
 
 
-def block_upsample(obj, upsampling_factor, axes=(-2, -1)):
+def block_upsample(obj, upsampling_factor, axes=(-2, -1), staggered=None):
     """Repeat each element f times along the given horizontal axes; an odd-size axis is an
-    interface axis whose last element is not repeated (cubedsphere/coarsen.py:843-897)."""
+    interface axis whose last element is not repeated (cubedsphere/coarsen.py:843-897).
+    ``staggered`` = (y, x) booleans overrides the reference's inference from odd sizes."""
     f = int(upsampling_factor)
     o, was_np = _to_dev(obj, floating=False)
     nd = o.dim()
@@ -184,6 +185,8 @@ def block_upsample(obj, upsampling_factor, axes=(-2, -1)):
     fy = f if (nd - 2) in axes else 1
     fx = f if (nd - 1) in axes else 1
     ys, xs = int(fy > 1 and cy % 2 == 1), int(fx > 1 and cx % 2 == 1)
+    if staggered is not None:
+        ys, xs = int(bool(staggered[0]) and fy > 1), int(bool(staggered[1]) and fx > 1)
     ny = (cy - 1) * fy + 1 if ys else cy * fy
     nx = (cx - 1) * fx + 1 if xs else cx * fx
     out = torch.empty(tuple(o.shape[:-2]) + (ny, nx), dtype=o.dtype, device=o.device)
@@ -312,6 +315,11 @@ def mask_weights(weights, p_coarse_on_fine, phalf_fine, mask_mode="phalf"):
     km = pf.shape[-3] - 1
     ncol = pf.shape[-2] * pf.shape[-1]
     lead = tuple(pf.shape[:-3])
+    want = lead + (km + 1 if mask_mode == "phalf" else km,) + tuple(pf.shape[-2:])
+    if mask_mode in ("phalf", "pfull") and tuple(pc.shape) != want:
+        raise ValueError(f"mask_weights: the coarse pressure must have shape {want}, got {tuple(pc.shape)}")
+    if tuple(w.shape[-2:]) != tuple(pf.shape[-2:]):
+        raise ValueError("mask_weights: weights and pressures must share their horizontal extents")
     nb0 = int(np.prod(lead, dtype=np.int64))
     w = w.expand(lead + tuple(w.shape[-2:])).contiguous()
     out = torch.empty(lead + (km,) + tuple(pf.shape[-2:]), dtype=w.dtype, device=w.device)
@@ -438,7 +446,7 @@ def _pressure_coarsen_unfused(fs, d, w, f, toa_pressure, mask_mode, iv, kord):
     (cubedsphere/regridz.py:31-220 + coarsen_restarts.py:528-534), one kernel each, bit-exact with
     the oracle.  Fine-size intermediates are materialised -- the fused kernels exist to avoid this."""
     dco = weighted_block_average(d, w[:, None], f)
-    dup = block_upsample(dco, f)
+    dup = block_upsample(dco, f, staggered=(False, False))  # cell centres, whatever the parity of the coarse extents
     phalf_c = pressure_at_interface(dup, toa_pressure)
     phalf_f = pressure_at_interface(d, toa_pressure)
     if mask_mode == "pfull":

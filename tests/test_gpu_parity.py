@@ -792,3 +792,52 @@ def test_pressure_coarsen_wide(core, oracle, f, n, mask_mode):
         assert eq(exact[0], oracle.weighted_block_average(reg["a"], masked, f))
     again, _ = core.pressure_coarsen(fields, delp, area, f, 300.0, mask_mode=mask_mode, mode=core.FAST)
     assert all(eq(a, b) for a, b in zip(fast, again))  # deterministic: fixed-order partial sums, no atomics
+
+
+# ------------------------------------------------------------------------------------------
+# full-size cases of BASELINE configs[3] and [4]
+# ------------------------------------------------------------------------------------------
+def test_c384_staggered_wind_round_trip(core, oracle):
+    """configs[3]: C384 u on y-interfaces [6, 79, 385, 384], edge-weighted block average with dx,
+    block_upsample_like back to the fine grid, and coarsening again."""
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(3)
+    nb, km, n, f = 6, 79, 384, 8
+    u = 10 * torch.randn((nb, km, n + 1, n), device=dev, generator=g)
+    dx = (2.0e4 + 8.8e3 * torch.rand((nb, n + 1, n), device=dev, generator=g))
+    uc = core.edge_weighted_block_average(u, dx[:, None], f, edge="x")
+    assert tuple(uc.shape) == (nb, km, n // f + 1, n // f)
+    # a slab against the oracle, bit for bit (tile 4, coarse rows 10..12 = fine lines 80, 88, 96)
+    sl = (slice(4, 5), slice(None), slice(80, 97), slice(None))
+    exp = oracle.edge_weighted_block_average(u[sl].cpu().numpy(), dx[4:5, None, 80:97].cpu().numpy(), f, edge="x")
+    assert eq(uc[4:5, :, 10:13].cpu().numpy(), exp)
+    up = core.block_upsample_like(uc, (n + 1, n))
+    assert tuple(up.shape) == tuple(u.shape)
+    assert torch.equal(up[:, :, ::f, ::f], uc) and torch.equal(up[:, :, 8, 5], uc[:, :, 1, 0])  # exact copies
+    assert torch.equal(up[:, :, -1, :], uc[:, :, -1, :].repeat_interleave(f, dim=-1))            # interface row: not repeated in y
+    again = core.edge_weighted_block_average(up, dx[:, None], f, edge="x")
+    assert float(((again - uc).abs() / (uc.abs() + 1e-3)).max()) < 1e-5  # mean of a constant window (fp32 rounding of sum(c*w)/sum(w))
+    # linearity: scaling by a power of two is exact
+    assert torch.equal(core.edge_weighted_block_average(u * 2, dx[:, None], f, edge="x"), uc * 2)
+
+
+def test_c3072_slab_factor_64(core):
+    """configs[4]: one (tile, coarse row) unit of C3072 -> C48: 64 fine rows x 3072 columns x 79 levels."""
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(4)
+    km, rows, n, f = 79, 64, 3072, 64
+    xx = torch.linspace(0, 6, n, device=dev)[None, :]
+    ps = (8.6e4 + 1.4e4 * torch.cos(xx * 1.1) + 1500 * torch.randn((1, rows, n), device=dev, generator=g)).clamp(5.0e4, 1.04e5)
+    b = torch.diff(torch.linspace(0, 1, km + 1, device=dev) ** 1.6)
+    delp = ((ps[:, None] - 300.0) * b[None, :, None, None] * (1 + 0.04 * (torch.rand((1, km, rows, n), device=dev, generator=g) - 0.5))).float()
+    area = (3.6e8 + 4.7e8 * torch.rand((1, rows, n), device=dev, generator=g)).float()
+    T = (180 + 140 * torch.rand((1, km, rows, n), device=dev, generator=g)).float()
+    ones = torch.ones_like(T)
+    (fT, f1), fdc = core.pressure_coarsen([T, ones], delp, area, f, 300.0, mode=core.FAST)
+    (eT, e1), edc = core.pressure_coarsen([T, ones], delp, area, f, 300.0, mode=core.EXACT)  # unfused operators
+    assert tuple(fT.shape) == (1, km, 1, n // f)
+    assert torch.equal(fdc, edc)
+    assert torch.equal(torch.isnan(fT), torch.isnan(eT))
+    ok = ~torch.isnan(eT)
+    assert float((fT[ok] - eT[ok]).abs().max()) <= 1e-6 * 320.0
+    assert float((f1[ok] - 1).abs().max()) <= 1e-6 and bool((e1[ok] == 1).all())
