@@ -19,7 +19,8 @@ reference's Beam pipeline fans out over timesteps the same way), then an NCCL al
 the small coarse outputs; time = max over ranks.
 
 Prints ONE JSON line.  `value` = fine grid points/s over all ranks with inputs resident in HBM;
-`e2e` = the same through the public API from pinned HOST buffers (H2D + kernel + D2H per step);
+`e2e` = the same through the public timestep driver from pinned HOST buffers (H2D + kernel + D2H
+per step, the upload of step i+1 overlapping the kernels and the download of step i);
 `roofline` = algorithmic bytes / CUDA-event time of the fused kernel vs the measured HBM copy
 bandwidth (MEASURED_PEAKS.json); `cpu_baseline` = the CPU oracle (numpy + C mappm restatement,
 all host cores) on a bounded sample of the same workload.
@@ -476,30 +477,40 @@ def main():
         h_delp = delp.cpu().pin_memory()
         h_area = area.cpu().pin_memory()
         h_fields = [x.cpu().pin_memory() for x in fields]
-        h_out = torch.empty((NFIELDS + 1, NTILE, KM, cdim, cdim), dtype=torch.float32).pin_memory()
         h2d = h_delp.numel() * 4 + h_area.numel() * 4 + sum(x.numel() * 4 for x in h_fields)
-        d2h = h_out.numel() * 4
+        d2h = (NFIELDS + 1) * NTILE * KM * cdim * cdim * 4
 
-        def e2e_step():
-            outs, dco = core.pressure_coarsen(h_fields, h_delp, h_area, FACTOR, TOA, mask_mode="phalf", mode=mode)
-            h_out.copy_(torch.stack(list(outs) + [dco]), non_blocking=True)
-            torch.cuda.synchronize()
+        # the public timestep driver (fv3net_b200/driver.py): every step uploads its inputs from pinned
+        # host memory and delivers its coarse outputs to pinned host memory; the upload of step i+1
+        # overlaps the kernels and the download of step i (two buffer sets).  The result of every
+        # step is read on the host (checksum) before its buffers are reused.
+        from fv3net_b200.driver import TimestepPipeline
+
+        pipe = TimestepPipeline(NFIELDS, NTILE, KM, NFINE, NFINE, FACTOR, TOA, mask_mode="phalf", mode=mode, depth=2)
+        checks = []
+
+        def e2e_run(n):
+            for cf, cd in pipe.run((h_fields, h_delp, h_area) for _ in range(n)):
+                checks.append(float(cd[0, 0, 0, 0]) + float(cf[0][0, 0, 0, 0]))
 
         n_e2e = max(3, min(args.steps, 5))
-        e2e_step()
+        e2e_run(2)
+        torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         t0 = time.perf_counter()
-        for _ in range(n_e2e):
-            e2e_step()
+        e2e_run(n_e2e)
+        torch.cuda.synchronize()
         e_ms = (time.perf_counter() - t0) * 1e3 / n_e2e
+        assert len(set(checks)) == 1, "the timestep driver returned different results for identical inputs"
+        del pipe
         if world > 1:
             t = torch.tensor([e_ms], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             e_ms = float(t.item())
         e2e = {"value": world * points_per_step() / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "ms_per_step": e_ms, "steps": n_e2e}
-        del h_delp, h_area, h_fields, h_out
+        del h_delp, h_area, h_fields
 
     if rank != 0:
         if world > 1:

@@ -841,3 +841,29 @@ def test_c3072_slab_factor_64(core):
     ok = ~torch.isnan(eT)
     assert float((fT[ok] - eT[ok]).abs().max()) <= 1e-6 * 320.0
     assert float((f1[ok] - 1).abs().max()) <= 1e-6 and bool((e1[ok] == 1).all())
+
+
+# ------------------------------------------------------------------------------------------
+# N3: the timestep driver (pinned, double-buffered H2D -> kernel -> D2H)
+# ------------------------------------------------------------------------------------------
+def test_timestep_pipeline(core):
+    from fv3net_b200.driver import TimestepPipeline
+
+    rng = np.random.default_rng(81)
+    nb, km, n, f, nf = 3, 12, 32, 8, 3
+    steps = []
+    for _ in range(5):
+        delp = torch.as_tensor(_synthetic_columns(rng, nb, km, n, np.float32)).pin_memory()
+        area = torch.as_tensor(rng.uniform(0.5, 1, size=(nb, n, n)).astype(np.float32)).pin_memory()
+        fields = [torch.as_tensor(rng.normal(size=(nb, km, n, n)).astype(np.float32)).pin_memory() for _ in range(nf)]
+        steps.append((fields, delp, area))
+    pipe = TimestepPipeline(nf, nb, km, n, n, f, 300.0, mode=core.FAST, depth=2)
+    got = [([x.clone() for x in cf], cd.clone()) for cf, cd in pipe.run(iter(steps))]
+    assert len(got) == 5
+    for (fields, delp, area), (cf, cd) in zip(steps, got):
+        ref, rdc = core.pressure_coarsen([x.cuda() for x in fields], delp.cuda(), area.cuda(), f, 300.0, mode=core.FAST)
+        assert torch.equal(cd, rdc.cpu())
+        for a, b in zip(cf, ref):
+            assert torch.equal(torch.nan_to_num(a), torch.nan_to_num(b.cpu()))
+    with pytest.raises(ValueError, match="expected 3 fields"):
+        pipe.submit(steps[0][0][:2], steps[0][1], steps[0][2])
