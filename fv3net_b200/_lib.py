@@ -26,7 +26,7 @@ EXPORTS = [
     "b200cs_blend", "b200cs_hydrostatic_balance", "b200cs_elementwise", "b200cs_compare_scalar",
     "b200cs_dominant_mask", "b200cs_pressure_at_midpoint_log", "b200cs_exposed_area_weights",
     "b200cs_pressure_coarsen_gather", "b200cs_pressure_coarsen_gather_workspace_bytes",
-    "b200cs_pressure_coarsen_wide", "b200cs_pressure_coarsen_wide_workspace_bytes",
+    "b200cs_pressure_coarsen_wide", "b200cs_pressure_coarsen_wide_workspace_bytes", "b200cs_mappm_fast",
 ]
 
 _lib = None
@@ -64,6 +64,7 @@ def load():
     lib.b200cs_mappm_workspace_bytes.restype = i64
     lib.b200cs_mappm.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, i64, i32, i32, i32, i32,
                                  vp, i64, vp]
+    lib.b200cs_mappm_fast.argtypes = [vp, p64, vp, p64, vp, p64, vp, p64, i64, i64, i32, i32, i32, i32, vp]
     lib.b200cs_pressure_coarsen.argtypes = [i32, pvp, i32, p64, vp, i32, p64, vp, i32, p64, pvp, vp, i64, i32,
                                             i64, i64, i32, i32, dbl, i32, i32, i32, i32, vp]
     lib.b200cs_pressure_coarsen_gather.argtypes = [i32, pvp, i32, p64, vp, i32, p64, vp, i32, p64, pvp, vp, i64, i32,

@@ -9,6 +9,8 @@ Every function launches hand-written sm_100a kernels through the C ABI of ``libb
 
 Reference citations are relative to /root/reference/external/vcm/vcm/.
 """
+import ctypes
+
 import numpy as np
 import torch
 
@@ -245,11 +247,12 @@ def pressure_at_interface(delp, toa_pressure=300.0, z_axis=-3):
     return _ret(out, was_np)
 
 
-def mappm(pe1, q1, pe2, i1=1, i2=None, iv=1, kord=1, ptop=0.0):
+def mappm(pe1, q1, pe2, i1=1, i2=None, iv=1, kord=1, ptop=0.0, mode=EXACT):
     """Drop-in for the f2py call ``mappm.mappm(pe1[ncol,km+1], q1[ncol,km], pe2[ncol,kn+1], i1,
     i2, iv, kord, ptop)`` -> float32 ``[ncol, kn]`` (external/mappm/mappm/mappm.f90:10;
     cubedsphere/regridz.py:329-334).  Scalars are coerced with int() like f2py does
-    (tests/test_mappm.py:9-13 passes floats); ptop is unused, as in the Fortran."""
+    (tests/test_mappm.py:9-13 passes floats); ptop is unused, as in the Fortran.  ``mode=FAST``:
+    b200cs_mappm_fast (kord <= 3 only), within 1e-6 relative of the default."""
     p1, was_np = _to_dev(pe1)
     q, _ = _to_dev(q1)
     p2, _ = _to_dev(pe2)
@@ -259,12 +262,17 @@ def mappm(pe1, q1, pe2, i1=1, i2=None, iv=1, kord=1, ptop=0.0):
         raise ValueError("mappm: expected pe1[ncol,km+1], q1[ncol,km], pe2[ncol,kn+1]")
     kn = p2.shape[1] - 1
     out = torch.empty((ncol, kn), dtype=torch.float32, device=q.device)
-    _mappm_raw(p1, (km + 1, 1), q, (km, 1), p2, (kn + 1, 1), out, (kn, 1), ncol, km, kn, int(iv), int(kord))
+    _mappm_raw(p1, (km + 1, 1), q, (km, 1), p2, (kn + 1, 1), out, (kn, 1), ncol, km, kn, int(iv), int(kord),
+               mode)
     return _ret(out, was_np)
 
 
-def _mappm_raw(p1, s1, q, sq, p2, s2, out, so, ncol, km, kn, iv, kord):
+def _mappm_raw(p1, s1, q, sq, p2, s2, out, so, ncol, km, kn, iv, kord, mode=EXACT):
     lib = _lib.load()
+    if mode == FAST:
+        _mappm_fast_raw(p1, (0,) + tuple(s1), q, (0,) + tuple(sq), p2, (0,) + tuple(s2), out, (0,) + tuple(so), 1, ncol, km,
+                        kn, iv, kord)
+        return
     ws, nbytes = None, 0
     if kord > 6:
         nbytes = lib.b200cs_mappm_workspace_bytes(ncol, km)
@@ -275,10 +283,18 @@ def _mappm_raw(p1, s1, q, sq, p2, s2, out, so, ncol, km, kn, iv, kord):
     _lib.check(rc, "mappm")
 
 
-def regrid_vertical(p_in, f_in, p_out, iv=1, kord=1, z_axis=-3):
+def _mappm_fast_raw(p1, s1, q, sq, p2, s2, out, so, nbatch, ncol, km, kn, iv, kord):
+    arr = lambda t: (ctypes.c_int64 * 3)(*t)  # noqa: E731
+    rc = _lib.load().b200cs_mappm_fast(p1.data_ptr(), arr(s1), q.data_ptr(), arr(sq), p2.data_ptr(), arr(s2),
+                                       out.data_ptr(), arr(so), nbatch, ncol, km, kn, iv, kord, _stream())
+    _lib.check(rc, "mappm_fast")
+
+
+def regrid_vertical(p_in, f_in, p_out, iv=1, kord=1, z_axis=-3, mode=EXACT):
     """cubedsphere/regridz.py:223-338 on arrays with the vertical axis at ``z_axis`` and all other
     axes equal.  The restart layout ``[..., z, y, x]`` is consumed in place through strides (no
-    transposes); output float32 like mappm's."""
+    transposes); output float32 like mappm's.  ``mode=FAST`` (kord <= 3, strictly increasing
+    ``p_out``) runs the throughput-oriented machine: within 1e-6 relative of EXACT."""
     pi, was_np = _to_dev(p_in)
     fi, _ = _to_dev(f_in)
     po, _ = _to_dev(p_out)
@@ -297,10 +313,14 @@ def regrid_vertical(p_in, f_in, p_out, iv=1, kord=1, z_axis=-3):
     oshape = list(fi.shape)
     oshape[z] = kn
     out = torch.empty(oshape, dtype=torch.float32, device=fi.device)
+    if mode == FAST and outer <= 65535:  # all slabs in one launch
+        _mappm_fast_raw(pi, ((km + 1) * inner, 1, inner), fi, (km * inner, 1, inner), po, ((kn + 1) * inner, 1, inner),
+                        out, (kn * inner, 1, inner), outer, inner, km, kn, int(iv), int(kord))
+        return _ret(out, was_np)
     for b in range(outer):  # each outer slab is a [z, inner] matrix: col stride 1, level stride inner
         off = lambda t, nz: t.view(outer, nz, inner)[b]  # noqa: E731
         _mappm_raw(off(pi, km + 1), (1, inner), off(fi, km), (1, inner), off(po, kn + 1), (1, inner),
-                   off(out, kn), (1, inner), inner, km, kn, int(iv), int(kord))
+                   off(out, kn), (1, inner), inner, km, kn, int(iv), int(kord), mode)
     return _ret(out, was_np)
 
 

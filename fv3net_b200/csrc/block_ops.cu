@@ -312,6 +312,32 @@ upsample_kernel(const T* __restrict__ in, T* __restrict__ out, int64_t nb, int64
     }
 }
 
+// VEC consecutive elements with the alignment of one 16-byte (32-byte for 4 doubles) access
+template <typename T, int N>
+struct alignas(sizeof(T) * N) Pack { T v[N]; };
+
+// Unstaggered windows whose width is a multiple of the 16-byte vector: one CTA per COARSE row; a
+// thread reads one coarse value and writes it as 16-byte stores into the fy fine rows below it
+// (fy * nx elements per CTA instead of nx: fewer, fatter CTAs and a quarter of the store
+// instructions).
+template <typename T, int VEC>
+__global__ void __launch_bounds__(128)
+upsample_rows_kernel(const T* __restrict__ in, T* __restrict__ out, int64_t rows, int64_t cx, int64_t nx, int fy,
+                     int fx) {
+    const int nv = (int)(nx / VEC);
+    for (int64_t crow = blockIdx.x; crow < rows; crow += gridDim.x) {
+        const T* src = in + crow * cx;
+        T* dst = out + crow * fy * nx;
+        for (int xv = threadIdx.x; xv < nv; xv += blockDim.x) {
+            const T sv = __ldg(src + (xv * VEC) / fx);
+            Pack<T, VEC> pk;
+#pragma unroll
+            for (int v = 0; v < VEC; v++) pk.v[v] = sv;
+            for (int r = 0; r < fy; r++) *reinterpret_cast<Pack<T, VEC>*>(dst + (int64_t)r * nx + (int64_t)xv * VEC) = pk;
+        }
+    }
+}
+
 // gathers columns 0, step, 2*step.. of [nb, ny, nx] into line-major [nb, nlines, ny]
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -350,19 +376,53 @@ pressure_interface_kernel(const T* __restrict__ delp, int64_t s0, int64_t sl, T*
     }
 }
 
-// grid = (column chunks, level, batch): no per-element index arithmetic, coalesced along columns
-template <typename TW, typename TP>
+// grid = (column chunks, level chunks, batch).  A thread owns VEC consecutive columns: the
+// surface pressure and the weight are loaded once and kept in registers while it walks kMwLevels
+// levels, each one vector load of the coarse pressure and one vector store.
+constexpr int kMwLevels = 8;
+
+template <typename TW, typename TP, int VEC>
 __global__ void __launch_bounds__(256)
 mask_weights_kernel(const TW* __restrict__ w, const TP* __restrict__ pc, const TP* __restrict__ pf,
                     TW* __restrict__ out, int64_t nb0, int64_t km, int64_t ncol, int mode) {
-    const int64_t k = blockIdx.y;
+    using PW = Pack<TW, VEC>;
+    using PP = Pack<TP, VEC>;
+    const int64_t k0 = (int64_t)blockIdx.y * kMwLevels;
+    const int64_t k1 = (k0 + kMwLevels < km) ? k0 + kMwLevels : km;
     for (int64_t b = blockIdx.z; b < nb0; b += gridDim.z) {
-        const TP* surf = pf + (b * (km + 1) + km) * ncol;
-        const TP* p = (mode == B200CS_MASK_PHALF) ? pc + (b * (km + 1) + k + 1) * ncol : pc + (b * km + k) * ncol;
-        const TW* wb = w + b * ncol;
-        TW* o = out + (b * km + k) * ncol;
-        for (int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; c < ncol; c += (int64_t)gridDim.x * blockDim.x)
-            o[c] = (mode == B200CS_MASK_NONE || p[c] < surf[c]) ? wb[c] : TW(0);
+        for (int64_t c = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) * VEC; c < ncol;
+             c += (int64_t)gridDim.x * blockDim.x * VEC) {
+            const PP surf = *reinterpret_cast<const PP*>(pf + (b * (km + 1) + km) * ncol + c);
+            const PW wv = *reinterpret_cast<const PW*>(w + b * ncol + c);
+            const TP* p = (mode == B200CS_MASK_PHALF) ? pc + (b * (km + 1) + k0 + 1) * ncol + c : pc + (b * km + k0) * ncol + c;
+            TW* o = out + (b * km + k0) * ncol + c;
+#pragma unroll 4
+            for (int64_t k = k0; k < k1; k++, p += ncol, o += ncol) {
+                PW r = wv;
+                if (mode != B200CS_MASK_NONE) {
+                    const PP pv = *reinterpret_cast<const PP*>(p);
+#pragma unroll
+                    for (int v = 0; v < VEC; v++) r.v[v] = (pv.v[v] < surf.v[v]) ? wv.v[v] : TW(0);
+                }
+                *reinterpret_cast<PW*>(o) = r;
+            }
+        }
+    }
+}
+
+template <typename TW, typename TP>
+static void launch_mask_weights(const void* w, const void* pc, const void* pf, void* out, int64_t nb0, int64_t km,
+                                int64_t ncol, int mode, cudaStream_t st) {
+    const unsigned gy = (unsigned)((km + kMwLevels - 1) / kMwLevels), gz = (unsigned)(nb0 < 65535 ? nb0 : 65535);
+    const uintptr_t bits = (uintptr_t)w | (uintptr_t)pc | (uintptr_t)pf | (uintptr_t)out;
+    if (ncol % 4 == 0 && (bits & (4 * sizeof(TP) - 1)) == 0 && (bits & (4 * sizeof(TW) - 1)) == 0) {
+        const int64_t gx = (ncol / 4 + 255) / 256;
+        mask_weights_kernel<TW, TP, 4><<<dim3((unsigned)(gx < 65535 ? gx : 65535), gy, gz), 256, 0, st>>>(
+            (const TW*)w, (const TP*)pc, (const TP*)pf, (TW*)out, nb0, km, ncol, mode);
+    } else {
+        const int64_t gx = (ncol + 255) / 256;
+        mask_weights_kernel<TW, TP, 1><<<dim3((unsigned)(gx < 65535 ? gx : 65535), gy, gz), 256, 0, st>>>(
+            (const TW*)w, (const TP*)pc, (const TP*)pf, (TW*)out, nb0, km, ncol, mode);
     }
 }
 
@@ -486,6 +546,16 @@ extern "C" int b200cs_block_upsample(const void* in, void* out, int elem_size, i
     const int64_t total = nb * ny * nx;
     if (total == 0) return B200CS_OK;
     cudaStream_t st = as_stream(stream);
+    const int vec = 16 / elem_size;
+    if (!y_staggered && !x_staggered && fx % vec == 0 && ((uintptr_t)out & 15) == 0) {
+        const int64_t rows = nb * cy;
+        const unsigned g = (unsigned)(rows < (1 << 30) ? rows : (1 << 30));
+        if (elem_size == 4)
+            upsample_rows_kernel<uint32_t, 4><<<g, 128, 0, st>>>((const uint32_t*)in, (uint32_t*)out, rows, cx, nx, fy, fx);
+        else
+            upsample_rows_kernel<uint64_t, 2><<<g, 128, 0, st>>>((const uint64_t*)in, (uint64_t*)out, rows, cx, nx, fy, fx);
+        return check_launch("block_upsample");
+    }
     if (elem_size == 4)
         upsample_kernel<uint32_t><<<(unsigned)(nb * ny < (1 << 30) ? nb * ny : (1 << 30)), 128, 0, st>>>((const uint32_t*)in, (uint32_t*)out, nb, cy, cx, ny, nx, fy, fx);
     else
@@ -536,16 +606,10 @@ extern "C" int b200cs_mask_weights(const void* w, int w_dtype, const void* pc, c
     const int64_t total = nb0 * km * ncol;
     if (total == 0) return B200CS_OK;
     cudaStream_t st = as_stream(stream);
-    B200CS_REQUIRE(km <= 65535, "mask_weights: km > 65535");
-    const dim3 g((unsigned)((ncol + 255) / 256 < 65535 ? (ncol + 255) / 256 : 65535), (unsigned)km, (unsigned)(nb0 < 65535 ? nb0 : 65535));
-    if (w_dtype == B200CS_F32 && p_dtype == B200CS_F32)
-        mask_weights_kernel<float, float><<<g, 256, 0, st>>>((const float*)w, (const float*)pc, (const float*)pf, (float*)out, nb0, km, ncol, mode);
-    else if (w_dtype == B200CS_F32 && p_dtype == B200CS_F64)
-        mask_weights_kernel<float, double><<<g, 256, 0, st>>>((const float*)w, (const double*)pc, (const double*)pf, (float*)out, nb0, km, ncol, mode);
-    else if (w_dtype == B200CS_F64 && p_dtype == B200CS_F32)
-        mask_weights_kernel<double, float><<<g, 256, 0, st>>>((const double*)w, (const float*)pc, (const float*)pf, (double*)out, nb0, km, ncol, mode);
-    else if (w_dtype == B200CS_F64 && p_dtype == B200CS_F64)
-        mask_weights_kernel<double, double><<<g, 256, 0, st>>>((const double*)w, (const double*)pc, (const double*)pf, (double*)out, nb0, km, ncol, mode);
+    if (w_dtype == B200CS_F32 && p_dtype == B200CS_F32) launch_mask_weights<float, float>(w, pc, pf, out, nb0, km, ncol, mode, st);
+    else if (w_dtype == B200CS_F32 && p_dtype == B200CS_F64) launch_mask_weights<float, double>(w, pc, pf, out, nb0, km, ncol, mode, st);
+    else if (w_dtype == B200CS_F64 && p_dtype == B200CS_F32) launch_mask_weights<double, float>(w, pc, pf, out, nb0, km, ncol, mode, st);
+    else if (w_dtype == B200CS_F64 && p_dtype == B200CS_F64) launch_mask_weights<double, double>(w, pc, pf, out, nb0, km, ncol, mode, st);
     else
         return set_err(B200CS_EINVAL, "mask_weights: dtype must be F32 or F64");
     return check_launch("mask_weights");

@@ -24,6 +24,7 @@ UNITS = [("status", "status.cu", ["-fmad=false"]),
          ("block_ops", "block_ops.cu", ["-fmad=false"]),
          ("stagger", "stagger.cu", ["-fmad=false"]),
          ("mappm", "mappm.cu", ["-fmad=false"]),
+         ("mappm_fast", "mappm_fast.cu", ["-fmad=true"]),
          ("column_ops", "column_ops.cu", ["-fmad=false"]),
          ("elementwise", "elementwise.cu", ["-fmad=false"]),
          ("pc_api", "pressure_coarsen_api.cu", ["-fmad=false"]),

@@ -483,9 +483,10 @@ def pressure_at_midpoint_log(delp, toa_pressure=TOA_PRESSURE, dim=COORD_Z_CENTER
     return _new(delp, res, delp.dims, _plain_coords(delp), name=delp.name, attrs=None)
 
 
-def regrid_vertical(p_in, f_in, p_out, iv=1, kord=1, z_dim_center="zaxis_1", z_dim_outer="zaxis_2"):
+def regrid_vertical(p_in, f_in, p_out, iv=1, kord=1, z_dim_center="zaxis_1", z_dim_outer="zaxis_2", mode=core.EXACT):
     """regridz.py:223-301: conservative PPM remap (mappm) of every column; float32 out like the
-    Fortran; dimension order and attributes of f_in."""
+    Fortran; dimension order and attributes of f_in.  ``mode`` is this library's addition
+    (core.FAST: 1e-6 arithmetic, kord <= 3)."""
     if z_dim_center == z_dim_outer:
         raise ValueError("'z_dim_center' and 'z_dim_outer' must not be equal.")
     dims_except_z = [d for d in f_in.dims if d != z_dim_center]
@@ -504,7 +505,7 @@ def regrid_vertical(p_in, f_in, p_out, iv=1, kord=1, z_dim_center="zaxis_1", z_d
         raise ValueError("All dimensions except vertical must be same size for p_in, f_in and p_out")
     if fi.shape[zax] != pi.shape[zax] - 1:
         raise ValueError("f_in must have a vertical dimension one shorter than p_in")
-    res = core.regrid_vertical(pi, fi, po, iv=iv, kord=kord, z_axis=zax)
+    res = core.regrid_vertical(pi, fi, po, iv=iv, kord=kord, z_axis=zax, mode=mode)
     coords = {k: cv for k, cv in _plain_coords(f_in).items() if z_dim_center not in cv[0]}
     return _new(f_in, res, f_in.dims, coords, name=f_in.name, attrs=f_in.attrs)
 

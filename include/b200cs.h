@@ -173,6 +173,21 @@ int b200cs_mappm(const float* pe1, int64_t pe1_cs, int64_t pe1_ls, const float* 
                  void* workspace, int64_t workspace_bytes, void* stream);
 
 /*
+ * mappm in B200CS_FAST arithmetic: the level search and the parabolas of MAPPM/mappm.f90:10-126,
+ * 614-931 with the pressure geometry hoisted, rcp.approx for its reciprocals and FMA contraction
+ * -- within 1e-6 relative of b200cs_mappm.  Only the lmt=0 profiles (kord <= 3; every reference
+ * caller passes kord=1, VCM/cubedsphere/regridz.py:227-228); pe2 must be strictly increasing.
+ * Other kord -> EINVAL.  No workspace.
+ * Batched: element (slab b, column c, level k) of an array lives at
+ * ptr[b*s[0] + c*s[1] + k*s[2]] (element strides), so the restart layout [tile, z, y, x] is ONE
+ * launch with s = {nz*ny*nx, 1, ny*nx} and the reference's [ncol, nz] is s = {0, nz, 1}, nbatch 1.
+ */
+int b200cs_mappm_fast(const float* pe1, const int64_t pe1_stride[3], const float* q1,
+                      const int64_t q1_stride[3], const float* pe2, const int64_t pe2_stride[3], float* q2,
+                      const int64_t q2_stride[3], int64_t nbatch, int64_t ncol, int km, int kn, int iv,
+                      int kord, void* stream);
+
+/*
  * Fused pressure-level coarse-graining.  Replaces, in ONE pass over the fine data,
  *   regrid_to_area_weighted_pressure (VCM/cubedsphere/regridz.py:31-78) =
  *     weighted_block_average(delp, w) -> block_upsample_like -> pressure_at_interface x2 ->

@@ -237,6 +237,29 @@ def test_mappm_all_kord_bitexact(core, oracle, kord):
         assert eq(core.mappm(pe1, q, pe2, iv=iv, kord=kord), oracle.mappm(pe1, q, pe2, iv=iv, kord=kord)), iv
 
 
+@pytest.mark.parametrize("iv", [-2, -1, 0, 1, 2])
+def test_mappm_fast_vs_exact(core, oracle, iv):
+    """b200cs_mappm_fast against the oracle on general grids (output columns that start above /
+    below the source top and end above / below its surface): 1e-6 of the column's range, the
+    tolerance BASELINE.json states for map1_ppm."""
+    rng = np.random.default_rng(40 + iv)
+    pe1, pe2 = _columns(rng, 4000, 79, 60)
+    pe2[::3] += 40.0     # first output edge inside the source column
+    pe2[1::7, 0] -= 200.0  # ... and above its top
+    q = rng.normal(size=(4000, 79)) * 50
+    q[::5] = np.abs(q[::5]) * 1e-3
+    want = oracle.mappm(pe1, q, pe2, iv=iv, kord=1)
+    got = core.mappm(pe1, q, pe2, iv=iv, kord=1, mode=core.FAST)
+    scale = np.abs(q).max(axis=1, keepdims=True)
+    assert np.all(np.abs(got - want) <= 1e-6 * scale + 1e-6 * np.abs(want))
+    # restart layout [z, ncol] through strides, same numbers
+    got_t = core.regrid_vertical(pe1.T.copy(), q.T.copy(), pe2.T.copy(), iv=iv, z_axis=0, mode=core.FAST)
+    assert eq(got_t.T, got)
+    from fv3net_b200._lib import B200csError
+    with pytest.raises(B200csError, match="kord"):
+        core.mappm(pe1, q, pe2, kord=9, mode=core.FAST)
+
+
 def test_regrid_vertical_layouts_and_errors(core, oracle):
     rng = np.random.default_rng(8)
     pe1, pe2 = _columns(rng, 6 * 4 * 5, 12, 9)

@@ -53,4 +53,6 @@ timeit("pressure_at_interface", lambda: core.pressure_at_interface(delp, 300.0),
 pi = core.pressure_at_interface(delp, 300.0)
 po = core.pressure_at_interface(delp * 1.01, 300.0)
 timeit("K7 regrid_vertical (mappm, kord=1) [z,y,x] in place", lambda: core.regrid_vertical(pi, T, po), 2 * nb * (km + 1) * n * n * E + 2 * fld)
-timeit("mask_weights", lambda: core.mask_weights(area, po, pi, "phalf"), 2 * nb * (km + 1) * n * n * E // 1 + fld)
+timeit("K7 regrid_vertical FAST (b200cs_mappm_fast)", lambda: core.regrid_vertical(pi, T, po, mode=core.FAST), 2 * nb * (km + 1) * n * n * E + 2 * fld)
+# reads coarse interfaces 1..km, the fine surface level and the weights; writes km levels
+timeit("mask_weights", lambda: core.mask_weights(area, po, pi, "phalf"), 2 * fld + nb * n * n * E + area.numel() * E)
