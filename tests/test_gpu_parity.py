@@ -163,6 +163,18 @@ def test_block_mode(core, oracle):
     exp = oracle.mode_reduce(an.reshape(6, 4, 4, 4, 4).transpose(0, 1, 3, 2, 4), axis=(3, 4), nan_policy="omit")
     got = core.block_reduce(an, 4, "mode", skipna=True)
     assert eq(got, np.asarray(exp, dtype=np.float64))
+    # 8x8 windows (register sorting network), float32, with and without NaNs; 3x3 (generic kernel)
+    b = rng.integers(0, 6, size=(5, 24, 48)).astype(np.float32)
+    bn = sprinkle_nans(rng, b, 0.3)
+    for f in (8, 4, 3):
+        blk = lambda x: x.reshape(5, 24 // f, f, 48 // f, f).transpose(0, 1, 3, 2, 4)  # noqa: E731
+        assert eq(core.block_reduce(b, f, "mode", skipna=False), oracle.mode_reduce(blk(b), axis=(3, 4)).astype(np.float32))
+        exp = np.asarray(oracle.mode_reduce(blk(bn), axis=(3, 4), nan_policy="omit"), dtype=np.float32)
+        assert eq(core.block_reduce(bn, f, "mode", skipna=True), exp)
+        c = rng.normal(size=(5, 24, 48)).astype(np.float32)
+        cn = sprinkle_nans(rng, c, 0.3)
+        assert eq(core.block_reduce(c, f, "median", skipna=False), np.median(blk(c), axis=(3, 4)))
+        assert eq(core.block_reduce(cn, f, "median", skipna=True), np.nanmedian(blk(cn), axis=(3, 4)))
     # block_edge_sum / block_edge_coarsen known answers, tests/test_cubedsphere.py:386-419
     d = np.array([[2, 6, 2], [6, 2, 6]])
     assert np.array_equal(core.block_reduce(d.T, 2, "sum", edge="x").T, [[8, 8]])
