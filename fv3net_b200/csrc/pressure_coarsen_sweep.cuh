@@ -68,30 +68,29 @@ __device__ __forceinline__ void sweep_read(const SweepCtx<NF>& c, int slot, floa
 constexpr int kStage = 8;  // per-thread staging ring of weighted output values (levels)
 
 // Fallback when a lane runs more than kStage levels ahead of the slowest lane of its warp (steep
-// terrain inside one 32-column row): one butterfly pass per distinct level, lanes of other levels
-// contributing zeros.  Only this warp touches its row's accumulators and within a pass every sum
-// is written by one lane, so plain read-modify-write suffices (a shared-memory float atomicAdd
-// compiles to a CAS loop).
+// terrain inside one 32-column row): the overflowing lanes add their values straight into the
+// row's accumulators.  Two lanes collide only when they belong to the same cell AND sit on the
+// same level; __match_any_sync groups those, and the members of a group take turns in lane order
+// (__syncwarp orders the read-modify-writes), so the sum is deterministic and needs no atomics
+// (a shared-memory float atomicAdd compiles to a CAS loop).  On rough terrain the levels of the
+// lanes are spread out and one or two turns suffice; the first version ran one butterfly pass
+// per distinct level (7.6 passes per edge, profiles/r01_sweep_rough_ncu.txt).
 template <int NF>
-__device__ __noinline__ void sweep_accumulate_slow(float* acc, int k, int lane, const float (&prod)[NF], bool on) {
+__device__ __noinline__ void sweep_accumulate_slow(float* acc, int k, int lane, float4 pv, bool on) {
     const unsigned full = 0xffffffffu;
     constexpr int kLevelStride = (kTileX / 8) * (NF + 1);
-    const int l8 = lane & 7;
-    const int slot = l8 < NF ? fast_owner<NF>(lane) : NF;
-    bool pending = on;
-    while (true) {
-        const unsigned kmin = __reduce_min_sync(full, pending ? (unsigned)k : 0xffffffffu);
-        if (kmin == 0xffffffffu) break;
-        const bool sel = pending && (unsigned)k == kmin;
-        float v[NF];
+    const unsigned key = on ? (((unsigned)(lane >> 3) << 16) | (unsigned)k) : (0x80000000u | (unsigned)lane);
+    const unsigned peers = __match_any_sync(full, key);
+    const int rank = __popc(peers & ((1u << lane) - 1u));
+    const int turns = (int)__reduce_max_sync(full, on ? (unsigned)rank + 1u : 0u);
+    float* dst = acc + k * kLevelStride;  // the weight sum of every level is formed in sweep_reduce, for all lanes
+    const float p[4] = {pv.x, pv.y, pv.z, pv.w};
+    for (int t = 0; t < turns; t++) {
+        if (on && rank == t) {
 #pragma unroll
-        for (int i = 0; i < NF; i++) v[i] = sel ? prod[i] : 0.f;
-        const float tot = reduce_fields8<NF>(v, lane);
-        if (l8 < NF) {  // the weight sum of every level is formed in sweep_reduce, for all lanes
-            float* dst = acc + kmin * kLevelStride + slot;
-            *dst = *dst + tot;
+            for (int i = 0; i < NF; i++) dst[i] = dst[i] + p[i];
         }
-        pending = pending && !sel;
+        __syncwarp(full);
     }
 }
 
@@ -110,12 +109,8 @@ __device__ __forceinline__ void sweep_stage(SweepCtx<NF>& c, const float (&o)[NF
     if (__any_sync(full, (chk != chk) || over)) {
 #pragma unroll
         for (int i = 0; i < 4; i++) prod[i] = nan_to_zero(prod[i]);
-        if (__any_sync(full, over)) {
-            float pn[NF];
-#pragma unroll
-            for (int i = 0; i < NF; i++) pn[i] = prod[i];
-            sweep_accumulate_slow<NF>(c.acc, c.k, c.lane, pn, over);
-        }
+        if (__any_sync(full, over))
+            sweep_accumulate_slow<NF>(c.acc, c.k, c.lane, make_float4(prod[0], prod[1], prod[2], prod[3]), over);
     }
     if (on && fits) c.buf[(c.k & (kStage - 1)) * kThreads] = make_float4(prod[0], prod[1], prod[2], prod[3]);
 }

@@ -457,6 +457,23 @@ def test_pressure_coarsen_fast_mode_tolerance(core, oracle, nfields, n):
         print(f"FAST vs EXACT nf={nfields} n={n} {mask_mode}: max |diff| / scale = {worst:.3e}")
 
 
+@pytest.mark.parametrize("nfields", [1, 2, 4])
+def test_pressure_coarsen_fast_rough_terrain(core, nfields):
+    """Surface pressure drawn independently per column (5e4..1.04e5 Pa): neighbouring columns of a
+    window sit on very different coarse levels, so lanes run far ahead of each other and the
+    staging ring of the layer-synchronous kernel overflows on most edges (its fallback path)."""
+    rng = np.random.default_rng(123 + nfields)
+    nb, km, n, f = 2, 79, 64, 8
+    ps = rng.uniform(5.0e4, 1.04e5, size=(nb, 1, n, n))
+    b = np.diff(np.linspace(0, 1, km + 1) ** 1.6)[None, :, None, None]
+    delp = ((ps - 300.0) * b * (1 + rng.uniform(-0.02, 0.02, size=(nb, km, n, n)))).astype(np.float32)
+    w = rng.uniform(3.6e8, 8.3e8, size=(nb, n, n)).astype(np.float32)
+    fields = [rng.uniform(180, 320, size=(nb, km, n, n)).astype(np.float32)]
+    fields += [(rng.normal(size=(nb, km, n, n)) * 10).astype(np.float32) for _ in range(nfields - 1)]
+    for mask_mode in ("phalf", "none"):
+        _fast_vs_exact(core, fields, delp, w, f, mask_mode=mask_mode)
+
+
 def test_pressure_coarsen_fast_smooth_fields_and_options(core, oracle):
     """smooth (realistic) profiles, every iv, pfull mask, NaN weights, edge lines"""
     rng = np.random.default_rng(5)
