@@ -64,29 +64,61 @@ def _collapse(shape, strides, lo, hi):
     return dims[-1][1]
 
 
+_CANON_CACHE = {}
+
+
+def _canon4_plan(layouts, lead_shape):
+    """(b0, b1, strides) for tensors given as (shape, stride) tuples, or None when some tensor
+    needs a contiguous copy first.  Pure integer work, memoised per layout."""
+    nl = len(lead_shape)
+    for split in range(nl, -1, -1):
+        strides = []
+        for shape, stride in layouts:
+            if stride[-1] != 1 and shape[-1] != 1:
+                break
+            s0 = _collapse(shape, stride, 0, split)
+            s1 = _collapse(shape, stride, split, nl)
+            if s0 is None or s1 is None:
+                break
+            strides.append((s0, s1, stride[-2]))
+        else:
+            b0 = int(np.prod(lead_shape[:split], dtype=np.int64))
+            b1 = int(np.prod(lead_shape[split:], dtype=np.int64))
+            return b0, b1, strides
+    return None
+
+
 def _canon4(ts, lead_shape):
     """Views tensors (all expanded to lead_shape + (ny, nx)) as [B0, B1, ny, nx] with common
     (B0, B1) and per-tensor element strides (s0, s1, sy).  Falls back to contiguous copies."""
-    nl = len(lead_shape)
     for attempt in range(2):
-        for split in range(nl, -1, -1):
-            ok, strides = True, []
-            for t in ts:
-                if t.stride(-1) != 1 and t.shape[-1] != 1:
-                    ok = False
-                    break
-                s0 = _collapse(t.shape, t.stride(), 0, split)
-                s1 = _collapse(t.shape, t.stride(), split, nl)
-                if s0 is None or s1 is None:
-                    ok = False
-                    break
-                strides.append((s0, s1, t.stride(-2)))
-            if ok:
-                b0 = int(np.prod(lead_shape[:split], dtype=np.int64))
-                b1 = int(np.prod(lead_shape[split:], dtype=np.int64))
-                return ts, b0, b1, strides
+        key = (tuple(lead_shape), tuple((tuple(t.shape), t.stride()) for t in ts))
+        plan = _CANON_CACHE.get(key, False)
+        if plan is False:
+            plan = _canon4_plan(key[1], lead_shape)
+            if len(_CANON_CACHE) < 4096:
+                _CANON_CACHE[key] = plan
+        if plan is not None:
+            return ts, plan[0], plan[1], plan[2]
         ts = [t.contiguous() for t in ts]
     raise AssertionError("unreachable")
+
+
+def _broadcast_lead(shapes):
+    """numpy broadcasting of the leading shapes (torch.broadcast_shapes costs ~20 us per call)."""
+    first = shapes[0]
+    if all(sh == first for sh in shapes[1:]):
+        return tuple(first)
+    n = max(len(sh) for sh in shapes)
+    out = [1] * n
+    for sh in shapes:
+        for i in range(1, len(sh) + 1):
+            d = sh[-i]
+            if d != 1:
+                if out[-i] not in (1, d):
+                    raise RuntimeError(f"shapes {[tuple(x) for x in shapes]} do not broadcast")
+                out[-i] = d
+    return tuple(out)
 
 
 def _window(f, edge):
@@ -113,11 +145,12 @@ def weighted_block_average(obj, weights, coarsening_factor, weights2=None, edge=
     v = _to_dev(weights2)[0] if weights2 is not None else None
     ny, nx = o.shape[-2:]
     tensors = [o, w] + ([v] if v is not None else [])
-    lead = torch.broadcast_shapes(*[t.shape[:-2] for t in tensors])
+    lead = _broadcast_lead([t.shape[:-2] for t in tensors])
     for t in tensors:
         if tuple(t.shape[-2:]) != (ny, nx):
             raise ValueError("obj and weights must share their horizontal extents")
-    tensors = [t.expand(lead + (ny, nx)) for t in tensors]
+    full = lead + (ny, nx)
+    tensors = [t if tuple(t.shape) == full else t.expand(full) for t in tensors]
     tensors, b0, b1, st = _canon4(tensors, lead)
     if edge is None and (ny % f or nx % f):
         raise ValueError(f"window {f} does not divide the horizontal extents {(ny, nx)}")
