@@ -72,46 +72,52 @@ __device__ __forceinline__ float4 ldg4(const float* p) {
 }
 
 // K1, wide windows (F = 16, 32, 64; fp32): nansum(obj * w) / nansum(w) over F x F blocks in
-// numpy's order (rowsum_numpy along x, rows added one after the other), streaming: one thread per
-// (window row, cell), CTA tile = F rows x 256 columns, every input line fully used out of L1.
-// C3072 -> C48 is factor 64 (workflows' coarsen_surface_c3072, BASELINE configs[4]).
+// numpy's order (rowsum_numpy along x, rows added one after the other), streaming.  numpy sums a
+// row of F <= 128 elements with eight interleaved accumulators r[j] += a[8m + j] and the tree
+// ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)).  TWO lanes share one (window row, cell): lane q keeps
+// accumulators 4q..4q+3, i.e. every second float4 of the row, so the chains need no shuffles and
+// the pair reads 32 contiguous bytes per load (a full sector; one lane per row touched 32
+// different lines per load instruction and was bound by L1 wavefronts at 30 % of HBM peak).
+// CTA tile = F rows x 128 columns.  C3072 -> C48 is factor 64 (workflows' coarsen_surface_c3072,
+// BASELINE configs[4]).
 template <int F>
 __global__ void __launch_bounds__(256)
 wba_wide_f32_kernel(const float* __restrict__ obj, int64_t so0, int64_t so1, int64_t soy,
                     const float* __restrict__ w, int64_t sw0, int64_t sw1, int64_t swy, float* __restrict__ out,
                     int64_t nb1, int64_t cyN, int64_t cxN) {
-    constexpr int NCX = 256 / F;  // cells per CTA
+    constexpr int NCX = 128 / F;  // cells per CTA
     __shared__ float s_num[NCX][F + 1], s_den[NCX][F + 1];
-    const int tid = threadIdx.x, r = tid / NCX, c = tid % NCX;
+    const int tid = threadIdx.x, q = tid & 1, pr = tid >> 1, r = pr / NCX, c = pr % NCX;
     const int64_t b0 = blockIdx.z / nb1, b1 = blockIdx.z % nb1;
     const int64_t cyg = blockIdx.y, cxg = (int64_t)blockIdx.x * NCX + c;
     float num = 0.f, den = 0.f;
     if (cxg < cxN) {
         const int64_t y = cyg * F + r, x0 = cxg * F;
-        const float4* dp = reinterpret_cast<const float4*>(obj + b0 * so0 + b1 * so1 + y * soy + x0);
-        const float4* wp = reinterpret_cast<const float4*>(w + b0 * sw0 + b1 * sw1 + y * swy + x0);
-        float rn[8], rd[8];
+        const float4* dp = reinterpret_cast<const float4*>(obj + b0 * so0 + b1 * so1 + y * soy + x0) + q;
+        const float4* wp = reinterpret_cast<const float4*>(w + b0 * sw0 + b1 * sw1 + y * swy + x0) + q;
+        float rn[4], rd[4];
 #pragma unroll
         for (int m = 0; m < F / 8; m++) {
-            const float4 d0 = __ldg(dp + 2 * m), d1 = __ldg(dp + 2 * m + 1);
-            const float4 w0 = __ldg(wp + 2 * m), w1 = __ldg(wp + 2 * m + 1);
-            const float dv[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
-            const float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+            const float4 d0 = __ldg(dp + 2 * m), w0 = __ldg(wp + 2 * m);
+            const float dv[4] = {d0.x, d0.y, d0.z, d0.w};
+            const float wv[4] = {w0.x, w0.y, w0.z, w0.w};
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
+            for (int j = 0; j < 4; j++) {
                 const float p = nan_to_zero(__fmul_rn(dv[j], wv[j]));
-                const float q = nan_to_zero(wv[j]);
+                const float z = nan_to_zero(wv[j]);
                 rn[j] = m == 0 ? p : __fadd_rn(rn[j], p);
-                rd[j] = m == 0 ? q : __fadd_rn(rd[j], q);
+                rd[j] = m == 0 ? z : __fadd_rn(rd[j], z);
             }
         }
-        num = __fadd_rn(__fadd_rn(__fadd_rn(rn[0], rn[1]), __fadd_rn(rn[2], rn[3])),
-                        __fadd_rn(__fadd_rn(rn[4], rn[5]), __fadd_rn(rn[6], rn[7])));
-        den = __fadd_rn(__fadd_rn(__fadd_rn(rd[0], rd[1]), __fadd_rn(rd[2], rd[3])),
-                        __fadd_rn(__fadd_rn(rd[4], rd[5]), __fadd_rn(rd[6], rd[7])));
+        num = __fadd_rn(__fadd_rn(rn[0], rn[1]), __fadd_rn(rn[2], rn[3]));
+        den = __fadd_rn(__fadd_rn(rd[0], rd[1]), __fadd_rn(rd[2], rd[3]));
     }
-    s_num[c][r] = num;
-    s_den[c][r] = den;
+    // (r0..r3) + (r4..r7): the odd lane's half is added onto the even lane's
+    const float num1 = __shfl_down_sync(0xffffffffu, num, 1), den1 = __shfl_down_sync(0xffffffffu, den, 1);
+    if (q == 0) {
+        s_num[c][r] = __fadd_rn(num, num1);
+        s_den[c][r] = __fadd_rn(den, den1);
+    }
     __syncthreads();
     if (tid < NCX) {
         const int64_t cx = (int64_t)blockIdx.x * NCX + tid;
@@ -126,7 +132,7 @@ wba_wide_f32_kernel(const float* __restrict__ obj, int64_t so0, int64_t so1, int
 template <int F>
 static int launch_wba_wide(const void* obj, const int64_t* so, const void* w, const int64_t* sw, void* out, int64_t nb0,
                            int64_t nb1, int64_t cy, int64_t cx, cudaStream_t st) {
-    dim3 grid((unsigned)((cx + 256 / F - 1) / (256 / F)), (unsigned)cy, (unsigned)(nb0 * nb1));
+    dim3 grid((unsigned)((cx + 128 / F - 1) / (128 / F)), (unsigned)cy, (unsigned)(nb0 * nb1));
     wba_wide_f32_kernel<F><<<grid, 256, 0, st>>>((const float*)obj, so[0], so[1], so[2], (const float*)w, sw[0], sw[1],
                                                 sw[2], (float*)out, nb1, cy, cx);
     return check_launch("weighted_block_average(wide f32)");

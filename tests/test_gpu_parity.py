@@ -267,6 +267,12 @@ def test_mappm_fast_vs_exact(core, oracle, iv):
     # restart layout [z, ncol] through strides, same numbers
     got_t = core.regrid_vertical(pe1.T.copy(), q.T.copy(), pe2.T.copy(), iv=iv, z_axis=0, mode=core.FAST)
     assert eq(got_t.T, got)
+    # [tile, z, y, x]: all slabs in one launch through the batch stride
+    p4 = np.ascontiguousarray(np.moveaxis(pe1.reshape(4, 20, 50, 80), -1, 1))
+    q4 = np.ascontiguousarray(np.moveaxis(q.reshape(4, 20, 50, 79), -1, 1))
+    o4 = np.ascontiguousarray(np.moveaxis(pe2.reshape(4, 20, 50, 61), -1, 1))
+    got4 = core.regrid_vertical(p4, q4, o4, iv=iv, z_axis=1, mode=core.FAST)
+    assert got4.shape == (4, 60, 20, 50) and eq(np.moveaxis(got4, 1, -1).reshape(4000, 60), got)
     from fv3net_b200._lib import B200csError
     with pytest.raises(B200csError, match="kord"):
         core.mappm(pe1, q, pe2, kord=9, mode=core.FAST)
