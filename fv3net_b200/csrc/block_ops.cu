@@ -352,8 +352,10 @@ struct OddEvenSort {
 template <typename T, int N>
 __device__ __forceinline__ void sort_network(T (&a)[N]) { OddEvenSort<T, N, 0, N>::run(a); }
 
-// VEC: window rows start on 16-byte boundaries and are read with 16-byte loads
-template <typename T, int F, bool VEC>
+// VEC: window rows start on 16-byte boundaries and are read with 16-byte loads.
+// SORT = false: sum / mean / min / max on the same register window (numpy's summation order:
+// pairwise tree for an 8-wide row, sequential below 8, rows added in order).
+template <typename T, int F, bool VEC, bool SORT>
 __global__ void __launch_bounds__(128)
 block_sort_kernel(const T* __restrict__ obj, int64_t s0, int64_t sy, T* __restrict__ out, int64_t nb, int64_t cy,
                   int64_t cx, int op, int skipna) {
@@ -382,13 +384,46 @@ block_sort_kernel(const T* __restrict__ obj, int64_t s0, int64_t sy, T* __restri
         }
         int n = 0;
 #pragma unroll
-        for (int q = 0; q < N; q++) {
-            const bool ok = (a[q] == a[q]);
-            n += ok ? 1 : 0;
-            a[q] = ok ? a[q] : (T)INFINITY;
-        }
-        sort_network<T, N>(a);
+        for (int q = 0; q < N; q++) n += (a[q] == a[q]) ? 1 : 0;
         T res;
+        if constexpr (!SORT) {
+            if (op == B200CS_OP_SUM || op == B200CS_OP_MEAN) {
+                T acc = T(0);
+#pragma unroll
+                for (int r = 0; r < F; r++) {
+                    T v[F];
+#pragma unroll
+                    for (int c = 0; c < F; c++) v[c] = skipna ? nan_to_zero(a[r * F + c]) : a[r * F + c];
+                    T rs;
+                    if constexpr (F == 8) {
+                        rs = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+                    } else {
+                        rs = T(0);
+#pragma unroll
+                        for (int c = 0; c < F; c++) rs += v[c];
+                    }
+                    acc += rs;
+                }
+                res = (op == B200CS_OP_SUM) ? acc : acc / (T)(skipna ? n : N);
+            } else {
+                T m = T(0);
+                bool any = false;
+#pragma unroll
+                for (int q = 0; q < N; q++) {
+                    const T v = a[q];
+                    const bool ok = (v == v);
+                    const bool take = ok && (!any || (op == B200CS_OP_MIN ? (v < m) : (v > m)));
+                    m = take ? v : m;
+                    any = any || ok;
+                }
+                res = ((n < N && !skipna) || !any) ? (T)NAN : m;
+            }
+            out[idx] = res;
+            continue;
+        }
+#pragma unroll
+        for (int q = 0; q < N; q++) a[q] = (a[q] == a[q]) ? a[q] : (T)INFINITY;
+        sort_network<T, N>(a);
         if ((n < N && !skipna) || n == 0) {
             res = (T)NAN;
         } else if (op == B200CS_OP_MEDIAN) {
@@ -426,14 +461,20 @@ static bool launch_block_sort(const T* obj, const int64_t s[2], T* out, int64_t 
     const unsigned g = (unsigned)blocks;
     constexpr int PV = 16 / (int)sizeof(T);
     const bool vec = f % PV == 0 && s[0] % PV == 0 && s[1] % PV == 0 && ((uintptr_t)obj & 15) == 0;
-#define B200CS_SORT_LAUNCH(F)                                                                                     \
-    (vec && (F) % PV == 0 ? block_sort_kernel<T, F, ((F) % PV == 0)><<<g, 128, 0, st>>>(obj, s[0], s[1], out, nb, cy, cx, op, skipna) \
-                          : block_sort_kernel<T, F, false><<<g, 128, 0, st>>>(obj, s[0], s[1], out, nb, cy, cx, op, skipna))
+    const bool sort = (op == B200CS_OP_MEDIAN || op == B200CS_OP_MODE);
+#define B200CS_SORT_LAUNCH1(F, V, S) block_sort_kernel<T, F, V, S><<<g, 128, 0, st>>>(obj, s[0], s[1], out, nb, cy, cx, op, skipna)
+#define B200CS_SORT_LAUNCH(F)                                                                      \
+    do {                                                                                           \
+        constexpr bool kV = ((F) % PV == 0);                                                       \
+        if (vec && kV) { if (sort) B200CS_SORT_LAUNCH1(F, kV, true); else B200CS_SORT_LAUNCH1(F, kV, false); } \
+        else { if (sort) B200CS_SORT_LAUNCH1(F, false, true); else B200CS_SORT_LAUNCH1(F, false, false); }     \
+    } while (0)
     if (f == 8) B200CS_SORT_LAUNCH(8);
     else if (f == 4) B200CS_SORT_LAUNCH(4);
     else if (f == 2) B200CS_SORT_LAUNCH(2);
     else return false;
 #undef B200CS_SORT_LAUNCH
+#undef B200CS_SORT_LAUNCH1
     return true;
 }
 
@@ -666,11 +707,11 @@ extern "C" int b200cs_block_reduce(const void* obj, int dtype, const int64_t s[2
     const int64_t total = nb * cy * cx;
     if (total == 0) return B200CS_OK;
     cudaStream_t st = as_stream(stream);
-    if ((op == B200CS_OP_MEDIAN || op == B200CS_OP_MODE) && !pad && fy == fx && ystep == fy && xstep == fx) {
+    if (!pad && fy == fx && ystep == fy && xstep == fx) {  // register-window kernels (2x2, 4x4, 8x8)
         const bool done = (dtype == B200CS_F32)
                               ? launch_block_sort<float>((const float*)obj, s, (float*)out, nb, cy, cx, fy, op, skipna, st)
                               : launch_block_sort<double>((const double*)obj, s, (double*)out, nb, cy, cx, fy, op, skipna, st);
-        if (done) return check_launch("block_reduce(sort network)");
+        if (done) return check_launch("block_reduce(register window)");
     }
     if (dtype == B200CS_F32)
         block_reduce_kernel<float><<<grid_for(total, 128), 128, 0, st>>>((const float*)obj, s[0], s[1], (float*)out,
