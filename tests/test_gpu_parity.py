@@ -210,6 +210,10 @@ def test_stagger_matches_xgcm_rule(core, oracle, dt):
     xs = np.swapaxes(oracle.stagger_delp(d, "x")[..., :, ::4], -1, -2)
     assert eq(core.stagger(d, "y", line_step=4), ys)
     assert eq(core.stagger(d, "x", line_step=4), np.ascontiguousarray(xs))
+    # sizes that are / are not a multiple of the 16-byte vector and of the 8-line band
+    for n in (20, 18, 24):
+        d = rng.uniform(3, 5, size=(6, 2, n, n)).astype(dt)
+        assert eq(core.stagger(d, "y"), oracle.stagger_delp(d, "y")), n
 
 
 def test_pressure_at_interface(core, oracle):
