@@ -445,7 +445,8 @@ def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.
         if mode == FAST and all_f32 and f in (16, 32, 64) and int(kord) <= 3 and fs:
             outs, dco = _pressure_coarsen_wide(fs, d, w, f, toa_pressure, mask_mode, iv, kord, return_delp_coarse)
         else:
-            outs, dco = _pressure_coarsen_unfused(fs, d, w, f, toa_pressure, mask_mode, iv, kord)
+            outs, dco = _pressure_coarsen_unfused(fs, d, w, f, toa_pressure, mask_mode, iv, kord,
+                                                  FAST if (mode == FAST and int(kord) <= 3) else EXACT)
         if was_np:
             return [o.cpu().numpy() for o in outs], (dco.cpu().numpy() if dco is not None else None)
         return outs, dco
@@ -494,10 +495,12 @@ def _pressure_coarsen_wide(fs, d, w, f, toa_pressure, mask_mode, iv, kord, retur
     return outs, dco
 
 
-def _pressure_coarsen_unfused(fs, d, w, f, toa_pressure, mask_mode, iv, kord):
+def _pressure_coarsen_unfused(fs, d, w, f, toa_pressure, mask_mode, iv, kord, remap_mode=EXACT):
     """Any factor, any dtype, every kord: the reference's own chain of operators
     (cubedsphere/regridz.py:31-220 + coarsen_restarts.py:528-534), one kernel each, bit-exact with
-    the oracle.  Fine-size intermediates are materialised -- the fused kernels exist to avoid this."""
+    the oracle.  Fine-size intermediates are materialised -- the fused kernels exist to avoid this.
+    ``remap_mode=FAST`` swaps only the remap for b200cs_mappm_fast (1e-6; coarse delp and masks
+    stay bit-exact)."""
     dco = weighted_block_average(d, w[:, None], f)
     dup = block_upsample(dco, f, staggered=(False, False))  # cell centres, whatever the parity of the coarse extents
     phalf_c = pressure_at_interface(dup, toa_pressure)
@@ -514,7 +517,7 @@ def _pressure_coarsen_unfused(fs, d, w, f, toa_pressure, mask_mode, iv, kord):
         masked = mask_weights(w, phalf_c, phalf_f, mask_mode)
     outs = []
     for x in fs:
-        reg = regrid_vertical(phalf_f, x, phalf_c, iv=iv, kord=kord)
+        reg = regrid_vertical(phalf_f, x, phalf_c, iv=iv, kord=kord, mode=remap_mode)
         outs.append(weighted_block_average(reg, masked, f))
     return outs, dco
 

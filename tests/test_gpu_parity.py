@@ -495,6 +495,20 @@ def test_pressure_coarsen_fast_rough_terrain(core, nfields):
         _fast_vs_exact(core, fields, delp, w, f, mask_mode=mask_mode)
 
 
+@pytest.mark.parametrize("f", [3, 6])
+def test_pressure_coarsen_fast_other_factors(core, f):
+    """factors without a fused kernel (C384 -> C128 is 3, -> C64 is 6): FAST swaps the remap of the
+    operator chain for b200cs_mappm_fast; coarse delp and masks stay bit-exact (_fast_vs_exact)"""
+    rng = np.random.default_rng(31 + f)
+    nb, km, n = 3, 40, 36
+    delp = _synthetic_columns(rng, nb, km, n, np.float32)
+    w = rng.uniform(3.6e8, 8.3e8, size=(nb, n, n)).astype(np.float32)
+    fields = [rng.uniform(180, 320, size=(nb, km, n, n)).astype(np.float32),
+              (rng.normal(size=(nb, km, n, n)) * 10).astype(np.float32)]
+    for mask_mode in ("phalf", "pfull", "none"):
+        _fast_vs_exact(core, fields, delp, w, f, mask_mode=mask_mode)
+
+
 def test_pressure_coarsen_fast_smooth_fields_and_options(core, oracle):
     """smooth (realistic) profiles, every iv, pfull mask, NaN weights, edge lines"""
     rng = np.random.default_rng(5)
