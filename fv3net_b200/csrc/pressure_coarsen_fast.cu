@@ -4,6 +4,7 @@
 
 #include "pressure_coarsen_fast.cuh"
 #include "pressure_coarsen_sweep.cuh"
+#include "pressure_coarsen_tma.cuh"
 
 namespace b200cs {
 bool pc_fast_covers(const PcArgs& a, int field_dtype, int p_dtype, int w_dtype) {
@@ -16,6 +17,12 @@ static bool use_v1() {
 }
 int pc_fast_entry(const PcArgs& a) {
     if (use_v1() && a.npeer == 0) return a.fy == 8 ? launch_pc_fast_fields<8>(a) : launch_pc_fast_fields<1>(a);
+    static const int tma_ctas = [] { const char* e = getenv("B200CS_TMA_CTAS"); return e ? atoi(e) : 3; }();  // dev switch: 0 = sweep kernel
+    if (tma_ctas > 0 && pc_tma_eligible(a)) {
+        // TMA-fed kernel; -1: the arrays cannot be described to TMA (alignment, strides) -> sweep kernel
+        const int rc = tma_ctas == 2 ? launch_pc_tma_fields<2>(a) : launch_pc_tma_fields<3>(a);
+        if (rc != -1) return rc;
+    }
     if (a.fy == 8) return launch_pc_sweep_fields<8>(a);
     return launch_pc_sweep_fields<1>(a);
 }

@@ -1,0 +1,709 @@
+// pressure_coarsen_tma.cuh -- K6, third design: the fused pressure-level coarse-graining kernel
+// fed by TMA (B200CS_FAST arithmetic, fp32 data, 8 x 8 windows, kord <= 3).  Replaces
+// regrid_to_area_weighted_pressure -> regrid_vertical/mappm -> _mask_weights ->
+// weighted_block_average (external/vcm/vcm/cubedsphere/regridz.py:31-220,
+// external/mappm/mappm/mappm.f90, external/vcm/vcm/cubedsphere/coarsen_restarts.py:485-534).
+//
+// Same dataflow and results as pressure_coarsen_sweep.cuh (coarse delp, interface pressures, masks
+// and the level search bit-identical to the EXACT kernel; values within 1e-6).  What is new
+// (profiles/r01_sweep_v8_ncu_summary.txt: issue-bound, 405 warp instructions per level):
+//
+//   * Every level of every array reaches shared memory as ONE 2-D TMA tile (cp.async.bulk.tensor,
+//     8 rows x 32 columns = 1 KB, 128-byte swizzle) issued by a single lane; completion is an
+//     mbarrier transaction count.  The per-thread LDGSTS, their 64-bit pointer arithmetic and the
+//     cp.async group bookkeeping are gone.  A slot of the 4-level ring is refilled by the LAST warp
+//     that releases it (shared-memory counter), so nobody ever waits for a free slot.
+//   * A warp owns HALF A COARSE CELL: 8 rows x 4 columns (one 16-byte chunk per row, which the
+//     128-byte swizzle spreads over all banks), two warps per cell.  All 32 lanes share the
+//     cell's level table (uniform loads) and the weighted values of an output level are summed
+//     over 32 lanes, not 8: accumulators shrink from [8 rows][km][4][NF+1] to [8 warps][km][NF+1]
+//     (50 KB -> 12.6 KB), which with 80 registers per thread admits 3 CTAs per SM.  Neighbouring
+//     columns of a compact 8 x 4 patch also sit on closer output levels than a 32-column strip.
+//   * The column machine works on PAIRS of fields with packed fp32 instructions and a clamp-form
+//     limiter (ppm_pack.cuh).
+//   * Phase A reads delp from TMA tiles too (8 levels per tile); one thread per (level, cell) forms
+//     the 64 products and adds them in numpy's order straight from shared memory.
+//   * NaN-skipping (xarray's coarsen().sum()) is checked once per reduced level on the warp total
+//     instead of once per staged value.
+#pragma once
+#include <cuda.h>
+
+#include "common.cuh"
+#include "ppm_pack.cuh"
+#include "pressure_coarsen_sweep.cuh"
+
+namespace b200cs {
+
+constexpr int kTmaSlots = 4;          // level ring depth
+constexpr int kTmaTile = 1024;        // bytes of one array-level tile (8 rows x 128 B)
+constexpr int kTmaKA = 8;             // Phase A: levels per delp tile
+constexpr int kTmaMaxArrays = 5;      // 4 fields + delp
+
+struct TmaMaps {
+    CUtensorMap lvl[kTmaMaxArrays];   // [NFL] fields, then delp: box (32, 8, 1, 1)
+    CUtensorMap dchunk;               // delp: box (32, 8, kTmaKA, 1)
+};
+
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "LAB_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE;\n"
+        "bra LAB_WAIT;\n"
+        "DONE:\n"
+        "}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load4(unsigned dst, const CUtensorMap* map, int x, int y, int z, int b, unsigned bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cta.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
+        ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(z), "r"(b), "r"(bar) : "memory");
+}
+
+// shared memory carve-up (bytes from the 1 KB-aligned base); fixed-size parts first so that the ring,
+// the barriers and the counters sit at compile-time offsets
+template <int NA>
+struct TmaSmem {
+    static constexpr int ring = 0;                                      // [4][NA] tiles
+    static constexpr int stage = ring + kTmaSlots * NA * kTmaTile;      // float4 [kStage][256]; Phase A: 4 delp tiles of 8 KB
+    static constexpr int w = stage + kStage * kThreads * 16;            // float [8][32] weights (NaN -> 0)
+    static constexpr int den = w + kTileY * kTileX * 4;                 // float [4] cell weight sums
+    static constexpr int cnt = den + 16;                                // unsigned [4] releases seen per slot
+    static constexpr int bar = cnt + 16;                                // u64 full[4], fullA[4]
+    static constexpr int lvl = bar + 64;                                // float4 [4][LS] level tables; then float acc[8][km][NV]
+};
+
+// keeps a cheap-to-recompute value in its register (ptxas rematerialises address arithmetic inside the hot loop)
+__device__ __forceinline__ unsigned opaque(unsigned v) {
+    unsigned r;
+    asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(v));
+    return r;
+}
+__device__ __forceinline__ float4 lds128(unsigned a) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts128(unsigned a, float4 v) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float lds32(unsigned a) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts32(unsigned a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
+
+// The level ring: slot s = level % 4 holds NA tiles (fields, then delp).
+template <int NA>
+struct TmaRing {
+    unsigned sb;          // shared address of the carve-up's base
+    unsigned nact;        // warps that consume the ring
+    __device__ __forceinline__ unsigned full(int slot) const { return sb + TmaSmem<NA>::bar + slot * 8; }
+    __device__ __forceinline__ unsigned tile(int slot, int i) const { return sb + TmaSmem<NA>::ring + (slot * NA + i) * kTmaTile; }
+    __device__ __forceinline__ void issue(const TmaMaps& maps, int slot, int level) const {
+        const unsigned bar = full(slot);
+        mbar_expect_tx(bar, NA * kTmaTile);
+#pragma unroll
+        for (int i = 0; i < NA; i++)
+            tma_load4(tile(slot, i), &maps.lvl[i], (int)(blockIdx.x * kTileX), (int)(blockIdx.y * kTileY), level, (int)blockIdx.z, bar);
+    }
+    // every lane of the warp has read its values of `level` from `slot`: the last warp to say so
+    // refills the slot with level + 4
+    // (the warp is converged at the shared loads, which therefore precede lane 0's atomic)
+    __device__ __forceinline__ void release(const TmaMaps& maps, int slot, int level, int km, int lane) const {
+        if (lane == 0) {
+            unsigned old;
+            asm volatile("atom.shared.inc.u32 %0, [%1], %2;" : "=r"(old) : "r"(sb + TmaSmem<NA>::cnt + slot * 4), "r"(nact - 1) : "memory");
+            if (old == nact - 1) {
+                if (level + kTmaSlots < km) issue(maps, slot, level + kTmaSlots);
+            }
+        }
+    }
+};
+
+template <int NP>
+struct TmaCtx {
+    PpmPack<NP> m;
+    float pacc;           // pe[] of the last consumed level + 1 (fp32 cumsum, as Phase A)
+    unsigned lvl;         // shared address of this warp's cell table: float4 [km + 1] {pb, 1/(pb-pt), threshold, coarse delp}
+    unsigned acc;         // shared address of this warp's accumulators: float [km][2 NP + 1]
+    unsigned buf;         // shared address of this thread's staging ring: float4 [kStage] (stride kThreads)
+    int k;                // next output level of this lane
+    int kdone;            // (warp-uniform) output levels below this one are reduced
+    int nanwin;           // > 0: a NaN level is inside this column's stencil, literal limiter tests
+    unsigned par;         // phase parity of ring slot 0 for the next level that lands there
+    unsigned accw;        // shared address this lane adds to when a level is reduced (its field's / the weight's slot of level kdone)
+    float pt, pb, rdpc, thr;
+    float wv, whalf, psurf, psmin;
+    int km, lane;
+};
+
+// sums 2 NP values over the 32 lanes of the warp; afterwards every lane holds the total of field
+// lane >> 3 (NP = 2) or lane >> 4 (NP = 1)
+template <int NP>
+__device__ __forceinline__ float reduce_fields32(float4 pv, int lane) {
+    const unsigned m = 0xffffffffu;
+    float t;
+    if (NP == 2) {
+        const bool hi = lane & 16;
+        const f2 p01 = f2_make(pv.x, pv.y), p23 = f2_make(pv.z, pv.w);
+        f2 keep = hi ? p23 : p01;
+        const f2 send = hi ? p01 : p23;
+        f2 recv = send;
+#if defined(__CUDA_ARCH__)
+        recv.v = __shfl_xor_sync(m, send.v, 16);
+#endif
+        keep = f2_add(keep, recv);
+        const bool b3 = lane & 8;
+        const float k0 = b3 ? f2_hi(keep) : f2_lo(keep), s0 = b3 ? f2_lo(keep) : f2_hi(keep);
+        t = k0 + __shfl_xor_sync(m, s0, 8);
+    } else {
+        const bool hi = lane & 16;
+        const float k0 = hi ? pv.y : pv.x, s0 = hi ? pv.x : pv.y;
+        t = k0 + __shfl_xor_sync(m, s0, 16);
+        t = t + __shfl_xor_sync(m, t, 8);
+    }
+    t = t + __shfl_xor_sync(m, t, 4);
+    t = t + __shfl_xor_sync(m, t, 2);
+    return t + __shfl_xor_sync(m, t, 1);
+}
+__device__ __forceinline__ float reduce_max32(float t) {
+    const unsigned m = 0xffffffffu;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t = fmaxf(t, __shfl_xor_sync(m, t, o));
+    return t;
+}
+__device__ __forceinline__ float reduce_all32(float t) {
+    const unsigned m = 0xffffffffu;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t = t + __shfl_xor_sync(m, t, o);
+    return t;
+}
+
+// Lanes that ran more than kStage levels ahead of the slowest lane of their warp add their values
+// straight into the accumulators (see sweep_accumulate_slow).  Called by exactly the lanes of
+// `mask`; those on the same level take turns in lane order, so the sum is deterministic.
+template <int NP>
+__device__ __noinline__ void tma_accumulate_slow(unsigned acc, int k, int lane, float4 pv, unsigned mask) {
+    constexpr int NV = 2 * NP + 1;
+    const unsigned peers = __match_any_sync(mask, (unsigned)k);
+    const int rank = __popc(peers & ((1u << lane) - 1u));
+    const int turns = (int)__reduce_max_sync(mask, (unsigned)rank + 1u);
+    const unsigned dst = acc + k * NV * 4;
+    const float p[4] = {nan_to_zero(pv.x), nan_to_zero(pv.y), nan_to_zero(pv.z), nan_to_zero(pv.w)};
+    for (int t = 0; t < turns; t++) {
+        if (rank == t) {
+#pragma unroll
+            for (int i = 0; i < 2 * NP; i++) sts32(dst + i * 4, lds32(dst + i * 4) + p[i]);
+        }
+        __syncwarp(mask);
+    }
+}
+
+template <int NP>
+__device__ __forceinline__ float4 unpack4(const f2 (&o)[NP]) {
+    if (NP == 2) return make_float4(f2_lo(o[0]), f2_hi(o[0]), f2_lo(o[NP - 1]), f2_hi(o[NP - 1]));
+    return make_float4(f2_lo(o[0]), f2_hi(o[0]), 0.f, 0.f);
+}
+
+// Reduces the staged levels every lane of the warp has passed: [c.kdone, min over lanes of k).
+// Lanes 0, 8, 16, 24 (NP = 2; 0 and 16 for NP = 1) end up with a field total, lane 1 adds the weight sum.
+template <int NP>
+__device__ __forceinline__ void tma_reduce(TmaCtx<NP>& c) {
+    const unsigned full = 0xffffffffu;
+    constexpr int NV = 2 * NP + 1;
+    const int kend = (int)__reduce_min_sync(full, (unsigned)c.k);
+    const bool writer = (c.lane == 1) || (NP == 2 ? ((c.lane & 7) == 0) : ((c.lane & 15) == 0));
+    for (int kk = c.kdone; kk < kend; kk++) {
+        const unsigned slot_p = c.buf + (kk & (kStage - 1)) * (kThreads * 16);
+        float4 pv = lds128(slot_p);
+        // a slot that holds no pending level reads as zero: a lane that overflowed the ring at
+        // level kk went through tma_accumulate_slow and must not be counted again
+        sts128(slot_p, make_float4(0.f, 0.f, 0.f, 0.f));
+        float tot = reduce_fields32<NP>(pv, c.lane);
+        if (__any_sync(full, tot != tot)) {  // NaN-skipping sums (xarray's coarsen().sum()): rare
+            pv.x = nan_to_zero(pv.x); pv.y = nan_to_zero(pv.y); pv.z = nan_to_zero(pv.z); pv.w = nan_to_zero(pv.w);
+            tot = reduce_fields32<NP>(pv, c.lane);
+        }
+        // the mask threshold of the level is the same for the 32 lanes; c.psmin = their smallest
+        // surface pressure: uniform test, no vote
+        const float thr = lds32(c.lvl + kk * 16 + 8);
+        float rd = c.whalf;
+        if (!(thr < c.psmin)) rd = reduce_all32(thr < c.psurf ? nan_to_zero(c.wv) : 0.f);
+        if (writer) sts32(c.accw, lds32(c.accw) + (c.lane == 1 ? rd : tot));
+        c.accw += NV * 4;
+    }
+    c.kdone = kend > c.kdone ? kend : c.kdone;
+}
+
+// output edges inside the current source layer (all remaining ones when it is the last layer):
+// each is evaluated once, its weighted values (mask and column weight folded into the scale) go
+// into the lane's staging ring -- NaNs are dealt with when the level is reduced
+template <int NP, bool LAST>
+__device__ __forceinline__ void tma_emit(TmaCtx<NP>& c) {
+    const unsigned full = 0xffffffffu;
+    while (true) {
+        // the level table ends with a +inf sentinel: lanes that are through never qualify
+        const bool can = LAST ? (c.k < c.km) : (c.pb <= c.m.pe_hi);
+        if (!__any_sync(full, can)) break;
+        const bool over = can && (c.k - c.kdone >= kStage);
+        const unsigned overmask = __ballot_sync(full, over);  // != 0: steep terrain inside the warp's patch, rare
+        if (can) {
+            f2 o[NP];
+            // 1/thickness, the column weight and the below-surface mask enter as one factor
+            // (MASK_NONE: thr = -inf; level 0: thr = +inf, see kernel)
+            const float scale = (c.thr < c.psurf) ? c.rdpc * c.wv : 0.f;
+            c.m.template edge<LAST>(c.pt, c.pb, scale, o);
+            if (over) tma_accumulate_slow<NP>(c.acc, c.k, c.lane, unpack4<NP>(o), overmask);
+            else sts128(c.buf + (c.k & (kStage - 1)) * (kThreads * 16), unpack4<NP>(o));
+            c.pt = c.pb;
+            c.k++;
+            const float4 lv = lds128(c.lvl + c.k * 16);
+            c.pb = lv.x; c.rdpc = lv.y; c.thr = lv.z;
+        }
+    }
+    if (!LAST) c.m.close(c.pt);
+    tma_reduce<NP>(c);
+}
+
+// this thread's values of one level: NFL fields (an odd count repeats the last one) and delp
+template <int NP, int NFL>
+__device__ __forceinline__ void tma_read(unsigned src, f2 (&q)[NP], float& d) {
+    float v[2 * NP];
+#pragma unroll
+    for (int i = 0; i < 2 * NP; i++) {
+        const int t = i < NFL ? i : NFL - 1;
+        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v[i]) : "r"(src + t * kTmaTile));
+    }
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(d) : "r"(src + NFL * kTmaTile));
+#pragma unroll
+    for (int p = 0; p < NP; p++) q[p] = f2_make(v[2 * p], v[2 * p + 1]);
+}
+
+// enter interior source layer L (PH = L%4; 1 <= L <= km-3)
+template <int NP, int NFL, int PH>
+__device__ __forceinline__ void tma_enter(TmaCtx<NP>& c, const TmaRing<NFL + 1>& rg, const TmaMaps& maps, unsigned src0, int L) {
+    f2 qn[NP];
+    if (L >= 2) {
+        // level L+2 lives in slot (PH+2)&3; slot 0 starts a new round of the ring
+        constexpr int slot = (PH + 2) & 3;
+        if (slot == 0) c.par ^= 1u;
+        float d;
+        mbar_wait(rg.full(slot), c.par);
+        tma_read<NP, NFL>(src0 + slot * (NFL + 1) * kTmaTile, qn, d);
+        rg.release(maps, slot, L + 2, c.km, c.lane);
+        c.pacc = c.pacc + nan_to_zero(d);
+        f2 s2 = qn[0];
+        if (NP == 2) s2 = f2_add(s2, qn[NP - 1]);
+        const float s = f2_lo(s2) + f2_hi(s2);
+        c.nanwin = (s != s) ? 5 : c.nanwin;  // NaN (or inf - inf) entering this column's stencil: rare
+    } else {  // L == 1: q[3] and pe[4] are left over from init()
+#pragma unroll
+        for (int p = 0; p < NP; p++) qn[p] = c.m.Q[3][p];
+    }
+    c.nanwin = c.nanwin > 0 ? c.nanwin - 1 : 0;
+    c.m.template step<PH>(c.pacc, qn, L == 1 || c.nanwin > 0);
+}
+
+template <int NFL>
+__device__ __forceinline__ void pc_gather_tail(const FieldPtrs<NFL>& fp, const float* delp_coarse, const PeerOut& peers,
+                                               int first, int64_t b0, int km, int64_t cyN, int64_t cxN, int tid) {
+    // The CTAs of one row of tiles (same blockIdx.y, b0) produce one complete coarse row.  The
+    // last of them to finish copies that row -- contiguous cxN-float segments, read back through
+    // L2 -- into this rank's slot on every peer with 16-byte stores over NVLink.
+    __shared__ int s_last;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        const int prev = atomicAdd(&peers.counters[b0 * gridDim.y + blockIdx.y], 1);
+        s_last = (prev == (int)gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const int64_t cy0 = blockIdx.y;  // kTileY / 8 = 1 coarse row per row of tiles
+    const bool vec = (cxN % 4 == 0);
+    const int64_t per_row = vec ? cxN / 4 : cxN;
+    const int64_t total = (int64_t)km * per_row;
+#pragma unroll
+    for (int sl = 0; sl <= NFL; sl++) {
+        const float* src = sl < NFL ? (const float*)fp.out[sl < NFL ? sl : 0] : delp_coarse;
+        if (sl == NFL && !(first == 0 && delp_coarse)) continue;
+        const int64_t slot = sl < NFL ? (first + sl) : peers.nfields;
+        for (int64_t e = tid; e < total; e += kThreads) {
+            const int64_t c = e % per_row;
+            const int64_t k = e / per_row;
+            if (cy0 >= cyN) continue;
+            const int64_t o = ((b0 * km + k) * cyN + cy0) * cxN;
+            if (vec) {
+                const float4 v = __ldcg(reinterpret_cast<const float4*>(src + o) + c);
+                for (int p = 0; p < peers.n; p++)
+                    reinterpret_cast<float4*>(peers.base[p] + slot * peers.field_elems + o)[c] = v;
+            } else {
+                const float v = __ldcg(src + o + c);
+                for (int p = 0; p < peers.n; p++) peers.base[p][slot * peers.field_elems + o + c] = v;
+            }
+        }
+    }
+}
+
+// CTAS: resident CTAs per SM the instance is compiled for (register cap: 3 -> 80, 2 -> 128)
+template <int NP, int NFL, int CTAS>
+__global__ void __launch_bounds__(kThreads, CTAS)
+pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL> fp,
+                            const float* __restrict__ w, int64_t ws0, int64_t wsy,
+                            float* __restrict__ delp_coarse, int km, int64_t ny, int64_t nx, float toa,
+                            int mask_mode, int iv, const __grid_constant__ PeerOut peers, int first) {
+    constexpr int NA = NFL + 1;
+    constexpr int NV = 2 * NP + 1;
+    constexpr int CW = kTileX / 8;  // cells per tile
+    using SM = TmaSmem<NA>;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int r = lane >> 2, c4 = lane & 3;
+    const int xl = wid * 4 + c4;  // column inside the tile: 16-byte chunk index = wid
+    const int64_t xg = (int64_t)blockIdx.x * kTileX + xl, yg = (int64_t)blockIdx.y * kTileY + r;
+    const int64_t b0 = blockIdx.z;
+    const int64_t cxN = nx / 8, cyN = ny / 8;
+    const bool active = xg < nx;  // ny % 8 == 0: rows are always inside
+    const unsigned my_off = (unsigned)(r * 128 + ((wid ^ r) << 4) + c4 * 4);
+
+    extern __shared__ __align__(1024) unsigned char smem_dyn[];
+    // the swizzle pattern of a tile is a function of the shared ADDRESS: 1 KB alignment by hand
+    unsigned char* smem_raw = smem_dyn + ((1024u - ((unsigned)__cvta_generic_to_shared(smem_dyn) & 1023u)) & 1023u);
+    // (volatile: ptxas otherwise re-derives the window address -- S2R SR_CgaCtaId + LEA -- at every use)
+    const unsigned sbase = opaque((unsigned)__cvta_generic_to_shared(smem_raw));
+    const int LS = sweep_lvl_stride(km);
+    float4* s_lvl = reinterpret_cast<float4*>(smem_raw + SM::lvl);            // [CW][LS], last = sentinel
+    float* s_acc = reinterpret_cast<float*>(s_lvl + (size_t)CW * LS);         // [8 warps][km][NV]
+    float* s_w = reinterpret_cast<float*>(smem_raw + SM::w);                  // [8][32]
+    float* s_den = reinterpret_cast<float*>(smem_raw + SM::den);              // [CW]
+    const unsigned bar_a = sbase + SM::bar + kTmaSlots * 8;
+
+    TmaRing<NA> rg;
+    rg.sb = sbase;
+    {
+        const int64_t left = nx - (int64_t)blockIdx.x * kTileX;
+        rg.nact = left >= kTileX ? 8u : (unsigned)(left / 8) * 2u;
+    }
+    const int nchunk = (km + kTmaKA - 1) / kTmaKA;
+    if (tid == 0) {
+#pragma unroll
+        for (int i = 0; i < 2 * kTmaSlots; i++) mbar_init(sbase + SM::bar + i * 8, 1);
+#pragma unroll
+        for (int i = 0; i < kTmaSlots; i++) sts32(sbase + SM::cnt + i * 4, 0.f);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        // Phase A's first four delp tiles, then levels 0..3 of the ring
+#pragma unroll
+        for (int cch = 0; cch < 4; cch++) {
+            if (cch < nchunk) {
+                mbar_expect_tx(bar_a + cch * 8, kTmaKA * kTmaTile);
+                tma_load4(sbase + SM::stage + cch * kTmaKA * kTmaTile, &maps.dchunk, (int)(blockIdx.x * kTileX),
+                          (int)(blockIdx.y * kTileY), cch * kTmaKA, (int)b0, bar_a + cch * 8);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < kTmaSlots; j++) rg.issue(maps, j, j);  // km >= 4
+    }
+    for (int t = tid; t < 8 * km * NV; t += kThreads) s_acc[t] = 0.f;
+
+    // ---------------- Phase A: coarse pressure levels of the tile's cells -------------------
+    const float wv = active ? __ldg(w + b0 * ws0 + yg * wsy + xg) : 0.f;
+    s_w[r * kTileX + xl] = nan_to_zero(wv);
+    const float whalf = reduce_all32(nan_to_zero(wv));
+    __syncthreads();  // barriers initialised, weights in shared memory
+    if (tid < CW) {   // weight sum of a cell: rows pairwise (numpy), then row after row
+        float d = 0.f;
+        for (int rr = 0; rr < 8; rr++) {
+            const float4 a = *reinterpret_cast<const float4*>(s_w + rr * kTileX + tid * 8);
+            const float4 b = *reinterpret_cast<const float4*>(s_w + rr * kTileX + tid * 8 + 4);
+            d = __fadd_rn(d, __fadd_rn(__fadd_rn(__fadd_rn(a.x, a.y), __fadd_rn(a.z, a.w)), __fadd_rn(__fadd_rn(b.x, b.y), __fadd_rn(b.z, b.w))));
+        }
+        s_den[tid] = d;
+    }
+    __syncthreads();
+    float pacc = toa;
+#pragma unroll 1
+    for (int ch = 0; ch < nchunk; ch++) {
+        const int bufi = ch & 3;
+        const unsigned tile = sbase + SM::stage + bufi * kTmaKA * kTmaTile;
+        mbar_wait(bar_a + bufi * 8, ((unsigned)ch >> 2) & 1u);
+        {   // fine surface pressure: sequential fp32 cumsum of the column (xarray cumsum == nancumsum)
+            float d[kTmaKA];
+#pragma unroll
+            for (int kk = 0; kk < kTmaKA; kk++) d[kk] = lds32(tile + kk * kTmaTile + my_off);
+#pragma unroll
+            for (int kk = 0; kk < kTmaKA; kk++) pacc = pacc + nan_to_zero(d[kk]);  // levels beyond km read as 0
+        }
+        if (wid == (ch & 7)) {
+            // one lane per (level, cell): 64 products delp*w in numpy's order (rows pairwise, then
+            // row after row), straight from the swizzled tile; bit-identical to the EXACT kernel
+            const int kk = lane >> 2, cc = lane & 3, k = ch * kTmaKA + kk;
+            const unsigned lt = tile + kk * kTmaTile;
+            float num = 0.f;
+#pragma unroll 2
+            for (int rr = 0; rr < 8; rr++) {
+                const float4 a = lds128(lt + rr * 128 + (((2 * cc) ^ rr) << 4));
+                const float4 b = lds128(lt + rr * 128 + (((2 * cc + 1) ^ rr) << 4));
+                const float4 wa = *reinterpret_cast<const float4*>(s_w + rr * kTileX + cc * 8);
+                const float4 wb = *reinterpret_cast<const float4*>(s_w + rr * kTileX + cc * 8 + 4);
+                float p0 = __fmul_rn(a.x, wa.x), p1 = __fmul_rn(a.y, wa.y), p2 = __fmul_rn(a.z, wa.z), p3 = __fmul_rn(a.w, wa.w);
+                float p4 = __fmul_rn(b.x, wb.x), p5 = __fmul_rn(b.y, wb.y), p6 = __fmul_rn(b.z, wb.z), p7 = __fmul_rn(b.w, wb.w);
+                float rs = __fadd_rn(__fadd_rn(__fadd_rn(p0, p1), __fadd_rn(p2, p3)), __fadd_rn(__fadd_rn(p4, p5), __fadd_rn(p6, p7)));
+                if (rs != rs) {  // NaN in delp: skipped (rare)
+                    p0 = nan_to_zero(p0); p1 = nan_to_zero(p1); p2 = nan_to_zero(p2); p3 = nan_to_zero(p3);
+                    p4 = nan_to_zero(p4); p5 = nan_to_zero(p5); p6 = nan_to_zero(p6); p7 = nan_to_zero(p7);
+                    rs = __fadd_rn(__fadd_rn(__fadd_rn(p0, p1), __fadd_rn(p2, p3)), __fadd_rn(__fadd_rn(p4, p5), __fadd_rn(p6, p7)));
+                }
+                num = __fadd_rn(num, rs);
+            }
+            if (k < km) {
+                const float dc = num / s_den[cc];
+                s_lvl[cc * LS + k].w = dc;
+                const int64_t cyg = blockIdx.y, cxg = (int64_t)blockIdx.x * CW + cc;
+                if (delp_coarse && cxg < cxN) delp_coarse[((b0 * km + k) * cyN + cyg) * cxN + cxg] = dc;
+            }
+        }
+        __syncthreads();  // everybody is through with this tile
+        if (tid == 0 && ch + 4 < nchunk) {
+            mbar_expect_tx(bar_a + bufi * 8, kTmaKA * kTmaTile);
+            tma_load4(tile, &maps.dchunk, (int)(blockIdx.x * kTileX), (int)(blockIdx.y * kTileY), (ch + 4) * kTmaKA, (int)b0, bar_a + bufi * 8);
+        }
+    }
+    // coarse interfaces: the cumsum is sequential (exact)
+    if (tid < CW) {
+        float pc = toa;
+        for (int k0 = 0; k0 < km; k0 += 8) {
+            float dc[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) dc[j] = (k0 + j < km) ? s_lvl[tid * LS + k0 + j].w : 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                if (k0 + j < km) {
+                    pc = pc + nan_to_zero(dc[j]);
+                    s_lvl[tid * LS + k0 + j].x = pc;
+                }
+            }
+        }
+    }
+    __syncthreads();  // coarse interface pressures are in s_lvl[].x
+    // per (cell, level): 1/thickness and the mask threshold, in parallel; sentinel entry; the
+    // staging ring (which Phase A borrowed) starts out as zeros
+    for (int t = tid; t < CW * (km + 1); t += kThreads) {
+        const int cc = t / (km + 1), k = t % (km + 1);
+        if (k == km) {
+            s_lvl[cc * LS + km] = make_float4(INFINITY, 0.f, INFINITY, 0.f);
+        } else {
+            const float4 e = s_lvl[cc * LS + k];
+            const float pn = e.x, dc = e.w;
+            const float pc = k > 0 ? s_lvl[cc * LS + k - 1].x : toa;
+            float thr = pn;  // PHALF: bottom interface of coarse layer k
+            if (mask_mode == B200CS_MASK_PFULL) thr = dc / (log(pn) - log(pc));
+            if (mask_mode == B200CS_MASK_NONE) thr = -INFINITY;  // always below the surface pressure
+            s_lvl[cc * LS + k].y = 1.0f / (pn - pc);
+            s_lvl[cc * LS + k].z = thr;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < kStage; j++) sts128(sbase + SM::stage + (j * kThreads + tid) * 16, make_float4(0.f, 0.f, 0.f, 0.f));
+    __syncthreads();
+
+    // ---------------- Phase B: layer-synchronous sweep ---------------------------------------
+    if (wid < (int)rg.nact) {  // warps of cells beyond nx have nothing to do (uniform per warp)
+        TmaCtx<NP> c;
+        c.km = km; c.lane = lane;
+        c.wv = wv; c.whalf = whalf; c.psurf = pacc;
+        c.lvl = sbase + SM::lvl + (wid >> 1) * LS * 16;
+        c.acc = sbase + SM::lvl + CW * LS * 16 + wid * km * NV * 4;
+        c.buf = sbase + SM::stage + tid * 16;
+        c.par = 0;
+        c.psmin = -reduce_max32(-pacc);
+        c.accw = c.acc + (lane == 1 ? 2 * NP : (NP == 2 ? (lane >> 3) : (lane >> 4))) * 4;
+        const unsigned src0 = opaque(sbase + SM::ring + my_off);
+        float4 v0;  // weighted level-0 values
+        {
+            f2 qA[NP], qB[NP], qC[NP], qD[NP];
+            float d0, d1, d2, d3, p[5];
+            mbar_wait(rg.full(0), 0); tma_read<NP, NFL>(src0 + 0 * NA * kTmaTile, qA, d0); rg.release(maps, 0, 0, km, lane);
+            mbar_wait(rg.full(1), 0); tma_read<NP, NFL>(src0 + 1 * NA * kTmaTile, qB, d1); rg.release(maps, 1, 1, km, lane);
+            mbar_wait(rg.full(2), 0); tma_read<NP, NFL>(src0 + 2 * NA * kTmaTile, qC, d2); rg.release(maps, 2, 2, km, lane);
+            mbar_wait(rg.full(3), 0); tma_read<NP, NFL>(src0 + 3 * NA * kTmaTile, qD, d3); rg.release(maps, 3, 3, km, lane);
+            p[0] = toa;
+            p[1] = p[0] + nan_to_zero(d0);
+            p[2] = p[1] + nan_to_zero(d1);
+            p[3] = p[2] + nan_to_zero(d2);
+            p[4] = p[3] + nan_to_zero(d3);
+            c.pacc = p[4];
+            float a[2 * NP], b[2 * NP], cc2[2 * NP], dd[2 * NP];
+            float s = 0.f;
+#pragma unroll
+            for (int i = 0; i < NP; i++) {
+                a[2 * i] = f2_lo(qA[i]); a[2 * i + 1] = f2_hi(qA[i]);
+                b[2 * i] = f2_lo(qB[i]); b[2 * i + 1] = f2_hi(qB[i]);
+                cc2[2 * i] = f2_lo(qC[i]); cc2[2 * i + 1] = f2_hi(qC[i]);
+                dd[2 * i] = f2_lo(qD[i]); dd[2 * i + 1] = f2_hi(qD[i]);
+                s += (a[2 * i] + a[2 * i + 1]) + (b[2 * i] + b[2 * i + 1]) + (cc2[2 * i] + cc2[2 * i + 1]) + (dd[2 * i] + dd[2 * i + 1]);
+            }
+            c.nanwin = (s != s) ? 5 : 0;
+            c.m.init(p, a, b, cc2, dd, iv);
+            // output level 0 copies the top source layer (mappm.f90:62-64): its weighted sums go
+            // straight into the accumulators; the edge that closes level 0 still runs (it opens
+            // level 1) but stages zeros because its threshold is +inf
+            const float4 lv = lds128(c.lvl);
+            const float wk0 = (lv.z < c.psurf) ? wv : 0.f;
+            v0 = make_float4(nan_to_zero(a[0] * wk0), nan_to_zero(a[1] * wk0), NP == 2 ? nan_to_zero(a[2 * NP - 2] * wk0) : 0.f,
+                             NP == 2 ? nan_to_zero(a[2 * NP - 1] * wk0) : 0.f);
+            c.k = 0; c.kdone = 0; c.pt = toa; c.pb = lv.x; c.rdpc = lv.y; c.thr = INFINITY;
+        }
+        {
+            const float tot = reduce_fields32<NP>(v0, lane);
+            const bool fwriter = NP == 2 ? ((lane & 7) == 0) : ((lane & 15) == 0);
+            if (fwriter) sts32(c.acc + (NP == 2 ? (lane >> 3) : (lane >> 4)) * 4, tot);  // accumulators start at zero
+        }
+        tma_emit<NP, false>(c);  // layer 0 (km >= 4: never the last)
+        // interior layers: the windows rotate by renaming (four instances of the layer step,
+        // selected by a uniform branch); the edge / staging / reduction code exists once
+#pragma unroll 1
+        for (int L = 1; L <= km - 3; L++) {
+            switch (L & 3) {
+                case 1: tma_enter<NP, NFL, 1>(c, rg, maps, src0, L); break;
+                case 2: tma_enter<NP, NFL, 2>(c, rg, maps, src0, L); break;
+                case 3: tma_enter<NP, NFL, 3>(c, rg, maps, src0, L); break;
+                default: tma_enter<NP, NFL, 0>(c, rg, maps, src0, L); break;
+            }
+            tma_emit<NP, false>(c);
+        }
+        // the two bottom layers, once, at phase 0 / 1
+        switch ((km - 2) & 3) {
+            case 1: c.m.template rotate_to0<1>(); break;
+            case 2: c.m.template rotate_to0<2>(); break;
+            case 3: c.m.template rotate_to0<3>(); break;
+            default: break;
+        }
+        c.m.template step_bottom<0>(iv);
+        tma_emit<NP, false>(c);
+        c.m.template step_last<1>();
+        tma_emit<NP, true>(c);
+    }
+    __syncthreads();
+
+    // ---------------- Phase C: the two halves of a cell, divide, store -----------------------
+    for (int t = tid; t < km * CW; t += kThreads) {
+        const int cc = t % CW, k = t / CW;
+        const int64_t cyg = blockIdx.y, cxg = (int64_t)blockIdx.x * CW + cc;
+        if (cxg < cxN) {
+            const float* a = s_acc + ((size_t)(2 * cc) * km + k) * NV;
+            const float* b = s_acc + ((size_t)(2 * cc + 1) * km + k) * NV;
+            const float den = a[2 * NP] + b[2 * NP];
+            const int64_t o = ((b0 * km + k) * cyN + cyg) * cxN + cxg;
+#pragma unroll
+            for (int i = 0; i < NFL; i++) ((float*)fp.out[i])[o] = (a[i] + b[i]) / den;
+        }
+    }
+
+    // ---------------- fused all-gather (b200cs_pressure_coarsen_gather) ----------------------
+    if (peers.n > 0) pc_gather_tail<NFL>(fp, delp_coarse, peers, first, b0, km, cyN, cxN, tid);
+}
+
+template <int NP, int NFL>
+size_t pressure_coarsen_tma_smem(int km) {
+    constexpr int NV = 2 * NP + 1, CW = kTileX / 8;
+    return (size_t)TmaSmem<NFL + 1>::lvl + (size_t)CW * sweep_lvl_stride(km) * sizeof(float4) +
+           sizeof(float) * (size_t)8 * km * NV + 1024;  // + alignment slack
+}
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+inline EncodeTiledFn tma_encode_fn() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+
+// [nb0, km, ny, nx] fp32 with element strides (s0, sl, sy, 1) as a rank-4 tensor map, box (32, 8, bz, 1)
+inline bool tma_encode_field(CUtensorMap* m, const void* base, int64_t nb0, int km, int64_t ny, int64_t nx,
+                             int64_t s0, int64_t sl, int64_t sy, int bz) {
+    EncodeTiledFn fn = tma_encode_fn();
+    if (!fn) return false;
+    if (nb0 == 1) s0 = sl * km;
+    if (((uintptr_t)base & 15) || sy <= 0 || sl <= 0 || s0 <= 0 || (sy & 3) || (sl & 3) || (s0 & 3)) return false;
+    const cuuint64_t dims[4] = {(cuuint64_t)nx, (cuuint64_t)ny, (cuuint64_t)km, (cuuint64_t)nb0};
+    const cuuint64_t strides[3] = {(cuuint64_t)sy * 4, (cuuint64_t)sl * 4, (cuuint64_t)s0 * 4};
+    const cuuint32_t box[4] = {(cuuint32_t)kTileX, (cuuint32_t)kTileY, (cuuint32_t)bz, 1};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// returns B200CS_OK, an error, or -1 when the arrays cannot be described to TMA (caller falls back)
+template <int NP, int NFL, int CTAS>
+int launch_pc_tma(const PcArgs& a, int first) {
+    auto kern = pressure_coarsen_tma_kernel<NP, NFL, CTAS>;
+    const size_t smem = pressure_coarsen_tma_smem<NP, NFL>(a.km);
+    if (smem > 227 * 1024) return -1;
+    TmaMaps maps;
+    for (int i = 0; i < NFL; i++)
+        if (!tma_encode_field(&maps.lvl[i], a.fields[first + i], a.nb0, a.km, a.ny, a.nx, a.fstride[0], a.fstride[1], a.fstride[2], 1)) return -1;
+    if (!tma_encode_field(&maps.lvl[NFL], a.delp, a.nb0, a.km, a.ny, a.nx, a.dstride[0], a.dstride[1], a.dstride[2], 1)) return -1;
+    if (!tma_encode_field(&maps.dchunk, a.delp, a.nb0, a.km, a.ny, a.nx, a.dstride[0], a.dstride[1], a.dstride[2], kTmaKA)) return -1;
+    for (int i = NFL + 1; i < kTmaMaxArrays; i++) maps.lvl[i] = maps.lvl[0];
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return set_err(B200CS_ECUDA, "pressure_coarsen(tma): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    FieldPtrs<NFL> fp;
+    for (int i = 0; i < NFL; i++) { fp.in[i] = a.fields[first + i]; fp.out[i] = a.out[first + i]; }
+    dim3 grid((unsigned)((a.nx + kTileX - 1) / kTileX), (unsigned)(a.ny / kTileY), (unsigned)a.nb0);
+    PeerOut po{};
+    po.n = a.npeer;
+    po.nfields = a.nfields;
+    po.field_elems = a.nb0 * a.km * (a.ny / 8) * (a.nx / 8);
+    po.counters = a.counters;
+    if (a.npeer > 0) {
+        cudaError_t em = cudaMemsetAsync(a.counters, 0, sizeof(int) * (size_t)grid.y * (size_t)a.nb0, a.st);
+        if (em != cudaSuccess) return set_err(B200CS_ECUDA, "pressure_coarsen_gather: cudaMemsetAsync: %s", cudaGetErrorString(em));
+    }
+    for (int p = 0; p < a.npeer && p < 8; p++) po.base[p] = (float*)a.peer[p];
+    kern<<<grid, kThreads, smem, a.st>>>(maps, fp, (const float*)a.w, a.wstride[0], a.wstride[1],
+                                         first == 0 ? (float*)a.delp_coarse : nullptr, a.km, a.ny, a.nx, (float)a.toa,
+                                         a.mask_mode, a.iv, po, first);
+    return check_launch("pressure_coarsen(tma)");
+}
+
+// the TMA kernel covers: what the sweep kernel covers, full 8 x 8 windows, numpy's pairwise window order
+inline bool pc_tma_eligible(const PcArgs& a) {
+    return a.fy == 8 && a.fx == 8 && a.seq == 0 && a.ny % 8 == 0 && a.nx % 8 == 0 && a.nx < (int64_t)1 << 31 &&
+           a.ny < (int64_t)1 << 31;
+}
+
+// fields [first, ...) in groups of 4 / 3 / 2 / 1; -1: not describable to TMA (nothing was launched)
+template <int CTAS>
+int launch_pc_tma_fields(const PcArgs& a) {
+    int first = 0;
+    while (first < a.nfields) {
+        const int left = a.nfields - first;
+        int rc, n;
+        if (left >= 4) { rc = launch_pc_tma<2, 4, CTAS>(a, first); n = 4; }
+        else if (left == 3) { rc = launch_pc_tma<2, 3, CTAS>(a, first); n = 3; }
+        else if (left == 2) { rc = launch_pc_tma<1, 2, CTAS>(a, first); n = 2; }
+        else { rc = launch_pc_tma<1, 1, CTAS>(a, first); n = 1; }
+        if (rc != B200CS_OK) return rc;
+        first += n;
+    }
+    return B200CS_OK;
+}
+
+}  // namespace b200cs

@@ -23,14 +23,14 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 RTOL = {"walk": 1e-6, "hybrid": 1e-6, "sigma": 3e-6, "wild": 3e-6}
 
 
-@pytest.fixture(scope="module", params=["fast", "sweep"])
+@pytest.fixture(scope="module", params=["fast", "sweep", "pack"])
 def harness(request):
     """both FAST column machines: ppm_fast.cuh (output-layer-major) and ppm_sweep.cuh
     (source-layer-major, the one the fast fused kernel runs)"""
     name = request.param
     src = os.path.join(HERE, "harness", f"ppm_{name}_host.cpp")
     so = os.path.join(HERE, "harness", f"libppm_{name}_host.so")
-    hdrs = [os.path.join(HERE, "..", "fv3net_b200", "csrc", h) for h in ("ppm_fast.cuh", "ppm_stream.cuh", "ppm_sweep.cuh")]
+    hdrs = [os.path.join(HERE, "..", "fv3net_b200", "csrc", h) for h in ("ppm_fast.cuh", "ppm_stream.cuh", "ppm_sweep.cuh", "ppm_pack.cuh")]
     if (not os.path.exists(so)) or max(os.path.getmtime(p) for p in [src] + hdrs) > os.path.getmtime(so):
         subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-x", "c++", src, "-o", so])
     lib = ctypes.CDLL(so)
