@@ -156,6 +156,41 @@ def cpu_reference_step(sample, nthreads):
     return outs
 
 
+SLAB_TILE, SLAB_ROWS = 2, (64, 80)  # tile 2, fine rows 64..79 = coarse rows 8, 9
+
+
+def check_fast_slab(outs, dco, fields, delp, area):
+    """Parity of the launch that is being timed: the FAST kernel's outputs for one slab of the bench
+    input (tile 2, two coarse rows, all 79 levels, all fields) against the CPU oracle run on that
+    slab.  Coarse delp must be bit-identical; fields within 1e-6 of sum|w x| / sum w of the coarse
+    cell and level (the oracle run on |x|), identical NaN patterns.  Returns the worst ratio."""
+    from oracle import vcm_ref as R
+
+    R.lib()
+    t, (r0, r1) = SLAB_TILE, SLAB_ROWS
+    c0, c1 = r0 // FACTOR, r1 // FACTOR
+    h = lambda x: x[t:t + 1, ..., r0:r1, :].cpu().numpy()
+    d, a, fs = h(delp), h(area), [h(x) for x in fields]
+    nthreads = os.cpu_count() or 1
+    names = [f"f{i}" for i in range(len(fs))]
+    reg, masked = R.regrid_to_area_weighted_pressure(dict(zip(names, fs)), d, a[:, None], TOA, FACTOR, False, nthreads=nthreads)
+    exp = [R.weighted_block_average(reg[k], masked, FACTOR) for k in names]
+    rega, _ = R.regrid_to_area_weighted_pressure({k: np.abs(x) for k, x in zip(names, fs)}, d, a[:, None], TOA, FACTOR, False,
+                                                 nthreads=nthreads)
+    scale = [R.weighted_block_average(rega[k], masked, FACTOR) for k in names]
+    edco = R.weighted_block_average(d, a[:, None], FACTOR)
+    got_d = dco[t:t + 1, :, c0:c1].cpu().numpy()
+    assert np.array_equal(got_d, edco, equal_nan=True), "coarse delp of the timed launch differs from the oracle"
+    worst = 0.0
+    for o, e, s_ in zip(outs, exp, scale):
+        g = o[t:t + 1, :, c0:c1].cpu().numpy().astype(np.float64)
+        e = e.astype(np.float64)
+        assert np.array_equal(np.isnan(g), np.isnan(e)), "NaN pattern of the timed launch differs from the oracle"
+        ok = ~np.isnan(e)
+        worst = max(worst, float((np.abs(g - e)[ok] / (s_.astype(np.float64)[ok] + 1e-300)).max()))
+    return worst
+
+
 def cpu_sample(seed):
     # one of the six tiles, all 79 levels, all 4 fields: 1/6 of the C384 workload
     delp, area, fields = synth_numpy(seed, ntile=1, km=KM, ny=NFINE, nx=NFINE)

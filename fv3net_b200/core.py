@@ -152,7 +152,9 @@ def weighted_block_average(obj, weights, coarsening_factor, weights2=None, edge=
     full = lead + (ny, nx)
     tensors = [t if tuple(t.shape) == full else t.expand(full) for t in tensors]
     tensors, b0, b1, st = _canon4(tensors, lead)
-    if edge is None and (ny % f or nx % f):
+    # xarray's coarsen(boundary="exact") raises when the window does not divide the coarsened axis
+    # (coarsen.py:210-213, 257-262); the interface axis of an edge average is subsampled, not coarsened
+    if (fy == ystep and ny % fy) or (fx == xstep and nx % fx):
         raise ValueError(f"window {f} does not divide the horizontal extents {(ny, nx)}")
     cy, cx = (ny - fy) // ystep + 1, (nx - fx) // xstep + 1
     odt = _promote(*tensors)
@@ -194,6 +196,9 @@ def block_reduce(obj, coarsening_factor, method="sum", skipna=True, edge=None, p
     if pad:
         cy, cx = -(-ny // fy), -(-nx // fx)
     else:
+        if (fy == ystep and ny % fy) or (fx == xstep and nx % fx):
+            raise ValueError(f"window {(fy, fx)} does not divide the horizontal extents {(ny, nx)}; pass pad=True "
+                             "for skimage's trailing-edge padding")
         cy, cx = (ny - fy) // ystep + 1, (nx - fx) // xstep + 1
     out = torch.empty(lead + (cy, cx), dtype=o.dtype, device=o.device)
     rc = _lib.load().b200cs_block_reduce(o.data_ptr(), _DT[o.dtype], _lib.i64arr((ny * nx, nx)), out.data_ptr(),
@@ -405,6 +410,8 @@ def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.
     f = int(coarsening_factor)
     was_np = not isinstance(delp, torch.Tensor)
     on_host = was_np or delp.device.type != "cuda"
+    if on_host and (out is not None or peer_ptrs is not None):
+        raise ValueError("pressure_coarsen: out= and peer_ptrs= name device buffers; pass device-resident inputs with them")
     if on_host and getattr(delp, "ndim", 0) == 4 and delp.shape[0] > 1 and len(fields) > 0:
         return _pressure_coarsen_from_host(fields, delp, weights, f, toa_pressure, mask_mode, edge_lines, iv, kord,
                                            mode, return_delp_coarse, seq_window, was_np)
@@ -434,6 +441,22 @@ def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.
             raise ValueError("pressure_coarsen: every field must have delp's shape")
     if tuple(w.shape) != (nb0, ny, nx):
         raise ValueError("pressure_coarsen: weights must be [B, ny, nx]")
+    # the reference loops over the variables of a dataset (coarsen_restarts.py:934-959): any number,
+    # including none.  The C ABI takes 1..B200CS_MAX_FIELDS fields per call.
+    if len(fs) == 0 or len(fs) > _lib.MAX_FIELDS:
+        if out is not None or peer_ptrs:
+            raise ValueError(f"pressure_coarsen: out= / peer_ptrs= need 1..{_lib.MAX_FIELDS} fields per call")
+        outs, dco = [], None
+        for i in range(0, len(fs), _lib.MAX_FIELDS):
+            o, dc = pressure_coarsen(fs[i:i + _lib.MAX_FIELDS], d, w, f, toa_pressure, mask_mode, edge_lines, iv, kord, mode,
+                                     return_delp_coarse and i == 0, seq_window)
+            outs += o
+            dco = dc if i == 0 else dco
+        if len(fs) == 0 and return_delp_coarse:
+            dco = weighted_block_average(d, w[:, None], f, edge="x" if edge_lines else None)
+        if was_np:
+            return [o.cpu().numpy() for o in outs], (dco.cpu().numpy() if dco is not None else None)
+        return outs, dco
     fy = 1 if edge_lines else f
     cy, cx = ny // fy, nx // f
     wdt = w.dtype

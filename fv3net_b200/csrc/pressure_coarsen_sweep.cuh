@@ -362,20 +362,27 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
     c.wv = wv; c.wrow = wrow; c.psurf = pacc;
     c.lvl = s_lvl + my_cell * LS;
     c.acc = s_acc + (size_t)ty * km * CW * NV + (lane / FX) * NV;  // own window row (shadow rows: unused cells)
+    // Rows beyond ny (edge-line launches: ny = n/f + 1 lines in tiles of 8) belong to no cell: their
+    // warps take part in the barriers and skip the sweep (uniform per warp).  They used to shadow
+    // the last row with zero weight -- with cells of zero weight, hence NaN levels, hence every
+    // output edge on the overflow path: time only, the results were discarded.
+    const bool row_ok = yg < ny;
     {
         float qA[NF], qB[NF], qC[NF], qD[NF], d0, d1, d2, d3, p[5];
         asm volatile("cp.async.wait_group 0;" ::: "memory");
-        sweep_read<NF>(c, 0, qA, d0);
-        sweep_read<NF>(c, 1, qB, d1);
-        sweep_read<NF>(c, 2, qC, d2);
-        sweep_read<NF>(c, 3, qD, d3);
-        p[0] = toa;
-        p[1] = p[0] + nan_to_zero(d0);
-        p[2] = p[1] + nan_to_zero(d1);
-        p[3] = p[2] + nan_to_zero(d2);
-        p[4] = p[3] + nan_to_zero(d3);
-        c.pacc = p[4];
-        c.m.init(p, qA, qB, qC, qD, iv);
+        if (row_ok) {
+            sweep_read<NF>(c, 0, qA, d0);
+            sweep_read<NF>(c, 1, qB, d1);
+            sweep_read<NF>(c, 2, qC, d2);
+            sweep_read<NF>(c, 3, qD, d3);
+            p[0] = toa;
+            p[1] = p[0] + nan_to_zero(d0);
+            p[2] = p[1] + nan_to_zero(d1);
+            p[3] = p[2] + nan_to_zero(d2);
+            p[4] = p[3] + nan_to_zero(d3);
+            c.pacc = p[4];
+            c.m.init(p, qA, qB, qC, qD, iv);
+        }
         __syncthreads();  // coarse interface pressures are in s_lvl[].x
         // per (cell, level): 1/thickness and the mask threshold, in parallel; sentinel entry; the
         // staging ring (which Phase A borrowed) starts out as zeros
@@ -397,15 +404,15 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
 #pragma unroll
         for (int j = 0; j < kStage; j++) s_buf[j * kThreads + tid] = make_float4(0.f, 0.f, 0.f, 0.f);
         __syncthreads();
-        sweep_issue<NF>(c, 0, 4 < km);
-        sweep_issue<NF>(c, 1, 5 < km);
-        // output level 0 copies the top source layer (mappm.f90:62-64): its weighted sums go
-        // straight into the accumulators; the edge that closes level 0 still runs (it opens level
-        // 1) but stages zeros because its threshold is +inf
-        const float4 lv = c.lvl[0];
-        c.k = 0; c.kdone = 0; c.pt = toa; c.pb = lv.x; c.rdpc = lv.y; c.thr = INFINITY;
-        c.buf = s_buf + tid;
-        {
+        if (row_ok) {
+            sweep_issue<NF>(c, 0, 4 < km);
+            sweep_issue<NF>(c, 1, 5 < km);
+            // output level 0 copies the top source layer (mappm.f90:62-64): its weighted sums go
+            // straight into the accumulators; the edge that closes level 0 still runs (it opens level
+            // 1) but stages zeros because its threshold is +inf
+            const float4 lv = c.lvl[0];
+            c.k = 0; c.kdone = 0; c.pt = toa; c.pb = lv.x; c.rdpc = lv.y; c.thr = INFINITY;
+            c.buf = s_buf + tid;
             const float wk0 = (lv.z < c.psurf) ? wv : 0.f;
             float v[NF];
 #pragma unroll
@@ -414,20 +421,22 @@ pressure_coarsen_sweep_kernel(FieldPtrs<NF> fp, int64_t fs0, int64_t fsl, int64_
             if ((lane & 7) < NF) c.acc[fast_owner<NF>(lane)] = tot;  // accumulators start at zero
         }
     }
-    sweep_emit<NF, false>(c);  // layer 0 (km >= 4: never the last)
-    // the windows rotate by renaming (four instances of the layer step, selected by a uniform
-    // branch); the edge / staging / reduction code exists once
+    if (row_ok) {
+        sweep_emit<NF, false>(c);  // layer 0 (km >= 4: never the last)
+        // the windows rotate by renaming (four instances of the layer step, selected by a uniform
+        // branch); the edge / staging / reduction code exists once
 #pragma unroll 1
-    for (int L = 1; L < km; L++) {
-        switch (L & 3) {
-            case 1: sweep_enter<NF, 1>(c, L, iv); break;
-            case 2: sweep_enter<NF, 2>(c, L, iv); break;
-            case 3: sweep_enter<NF, 3>(c, L, iv); break;
-            default: sweep_enter<NF, 0>(c, L, iv); break;
+        for (int L = 1; L < km; L++) {
+            switch (L & 3) {
+                case 1: sweep_enter<NF, 1>(c, L, iv); break;
+                case 2: sweep_enter<NF, 2>(c, L, iv); break;
+                case 3: sweep_enter<NF, 3>(c, L, iv); break;
+                default: sweep_enter<NF, 0>(c, L, iv); break;
+            }
+            if (L < km - 1) sweep_emit<NF, false>(c);
         }
-        if (L < km - 1) sweep_emit<NF, false>(c);
+        sweep_emit<NF, true>(c);
     }
-    sweep_emit<NF, true>(c);
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
 

@@ -55,12 +55,22 @@ def pressure_coarsen_sharded(fields, delp, weights, coarsening_factor, toa_press
         rows = slice(cy0 * f, cy1 * f)
         outs, dco = compute([x[tile:tile + 1, :, rows] for x in fields], delp[tile:tile + 1, :, rows],
                             weights[tile:tile + 1, rows], f, toa_pressure, mask_mode=mask_mode, **kw)
-        t = torch.stack([torch.as_tensor(o) for o in list(outs) + [dco]])  # [nf+1, 1, km, rows, ncx]
+        parts = [torch.as_tensor(o) for o in list(outs) + [dco]]
+        dt = parts[0].dtype
+        for q in parts[1:]:  # fp32 weights with fp64 delp: coarse fields are fp32, coarse delp fp64
+            dt = torch.promote_types(dt, q.dtype)
+        t = torch.stack([q.to(dt) for q in parts])                          # [nf+1, 1, km, rows, ncx]
         pieces.append(t[:, 0].permute(2, 0, 1, 3))                          # [rows, nf+1, km, ncx]
     dev = pieces[0].device if pieces else (delp.device if isinstance(delp, torch.Tensor) else torch.device("cpu"))
-    mine = torch.zeros((per, nf + 1, km, ncx), dtype=torch.float32, device=dev)
+    # every rank derives the gathered dtype from the inputs alone (ranks without units must agree)
+    gdt = torch.float32
+    for q in list(fields) + [delp, weights]:
+        qd = q.dtype if isinstance(q, torch.Tensor) else torch.as_tensor(q[:0]).dtype
+        if qd == torch.float64:
+            gdt = torch.float64
+    mine = torch.zeros((per, nf + 1, km, ncx), dtype=gdt, device=dev)
     if pieces:
-        mine[: hi - lo] = torch.cat(pieces).to(torch.float32)
+        mine[: hi - lo] = torch.cat(pieces).to(gdt)
     if world > 1:
         gathered = torch.empty((world * per,) + tuple(mine.shape[1:]), dtype=mine.dtype, device=dev)
         dist.all_gather_into_tensor(gathered, mine, group=group)
