@@ -43,6 +43,8 @@ TOA = 300.0
 METRIC = "fine grid pts/s, C384->C48 pressure-level coarsening (delp + 4 fields, 6 tiles x 79 levels)"
 UNIT = "fine grid points/s"
 FALLBACK_HBM_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md fallback
+WORKLOAD = ("C384->C48 pressure-level fv_core A-grid (delp + W,T,ua,va): 6 tiles x 79 levels x 384 x 384 fp32, f=8, "
+            "kord=1, iv=1, extrapolate=False")
 
 
 def algorithmic_bytes(ntile=NTILE, km=KM, n=NFINE, f=FACTOR, nf=NFIELDS, elt=4):
@@ -72,16 +74,46 @@ def synth_numpy(seed, ntile=NTILE, km=KM, ny=NFINE, nx=NFINE):
     return delp, area, fields
 
 
-def synth_device(torch, seed, dev):
+def surface_pressure(torch, terrain, g, dev, ntile=NTILE, n=NFINE):
+    """Synthetic fine surface pressure [ntile, n, n] (Pa).
+    smooth:    SURVEY.md 8d -- a smooth field + 1.5 kPa of white noise (BASELINE's workload).
+    orography: a smooth base with a few Gaussian mountain ranges per tile, up to 45 kPa high and
+               4..10 columns wide: slopes of 3 kPa and more per column, Andes / Himalaya-like, i.e.
+               neighbouring columns of one coarse cell sit on very different coarse levels.
+    rough:     drawn independently per column from U(50, 104) kPa -- rougher than any terrain; the
+               worst case of the layer-synchronous kernel (its lanes drift apart by tens of levels)."""
+    yy = torch.linspace(0, 6, n, device=dev)[:, None]
+    xx = torch.linspace(0, 6, n, device=dev)[None, :]
+    if terrain == "rough":
+        return 5.0e4 + 5.4e4 * torch.rand((ntile, n, n), device=dev, generator=g)
+    if terrain == "orography":
+        ps = 1.0e5 - 2.0e3 * torch.sin(yy * 1.3) * torch.cos(xx * 1.1) + 200 * torch.randn((ntile, n, n), device=dev, generator=g)
+        iy = torch.arange(n, device=dev, dtype=torch.float32)[:, None]
+        ix = torch.arange(n, device=dev, dtype=torch.float32)[None, :]
+        prm = torch.rand((ntile, 6, 5), device=dev, generator=g)
+        for t in range(ntile):
+            for m in range(6):
+                cy, cx, amp, sg, el = (float(v) for v in prm[t, m])
+                sig = 4.0 + 6.0 * sg
+                # an elongated range: 1 : (1 + 3 el) aspect ratio
+                d2 = ((iy - cy * n) / sig) ** 2 + ((ix - cx * n) / (sig * (1 + 3 * el))) ** 2
+                ps[t] -= (2.5e4 + 2.0e4 * amp) * torch.exp(-0.5 * d2)
+        return ps.clamp(5.0e4, 1.04e5)
+    ps = 8.6e4 + 1.4e4 * torch.sin(yy * 1.3) * torch.cos(xx * 1.1) + 1500 * torch.randn((ntile, n, n), device=dev, generator=g)
+    return ps.clamp(5.0e4, 1.04e5)
+
+
+def synth_delp(torch, ps, g, dev):
+    b = torch.diff(torch.linspace(0, 1, KM + 1, device=dev) ** 1.6)
+    noise = 1 + 0.04 * (torch.rand((ps.shape[0], KM) + tuple(ps.shape[1:]), device=dev, generator=g) - 0.5)
+    return ((ps[:, None] - TOA) * b[None, :, None, None] * noise).float().contiguous()
+
+
+def synth_device(torch, seed, dev, terrain="smooth"):
     """Same distribution generated on the device (generating 1.4 GB with numpy would dominate the run)."""
     g = torch.Generator(device=dev).manual_seed(seed)
-    yy = torch.linspace(0, 6, NFINE, device=dev)[:, None]
-    xx = torch.linspace(0, 6, NFINE, device=dev)[None, :]
-    ps = 8.6e4 + 1.4e4 * torch.sin(yy * 1.3) * torch.cos(xx * 1.1) + 1500 * torch.randn((NTILE, NFINE, NFINE), device=dev, generator=g)
-    ps = ps.clamp(5.0e4, 1.04e5)
-    b = torch.diff(torch.linspace(0, 1, KM + 1, device=dev) ** 1.6)
-    noise = 1 + 0.04 * (torch.rand((NTILE, KM, NFINE, NFINE), device=dev, generator=g) - 0.5)
-    delp = ((ps[:, None] - TOA) * b[None, :, None, None] * noise).float().contiguous()
+    ps = surface_pressure(torch, terrain, g, dev)
+    delp = synth_delp(torch, ps, g, dev)
     area = (3.6e8 + 4.7e8 * torch.rand((NTILE, NFINE, NFINE), device=dev, generator=g)).float()
     fields = [(180 + 140 * torch.rand((NTILE, KM, NFINE, NFINE), device=dev, generator=g)).float()]
     fields += [(10 * torch.randn((NTILE, KM, NFINE, NFINE), device=dev, generator=g)).float() for _ in range(NFIELDS - 1)]
@@ -191,14 +223,29 @@ def check_fast_slab(outs, dco, fields, delp, area):
     return worst
 
 
-def cpu_sample(seed):
-    # one of the six tiles, all 79 levels, all 4 fields: 1/6 of the C384 workload
-    delp, area, fields = synth_numpy(seed, ntile=1, km=KM, ny=NFINE, nx=NFINE)
-    pts = 1 * KM * NFINE * NFINE * NFIELDS
-    return (delp, area, fields), pts, "1 tile x 79 levels x 384 x 384 columns x 4 fields (1/6 of the C384 workload)"
+def cpu_sample(seed, ntile=1, ny=NFINE):
+    delp, area, fields = synth_numpy(seed, ntile=ntile, km=KM, ny=ny, nx=NFINE)
+    pts = ntile * KM * ny * NFINE * NFIELDS
+    frac = ntile * ny / (NTILE * NFINE)
+    desc = f"{ntile} tile(s) x 79 levels x {ny} x 384 columns x 4 fields" + \
+        (" (the whole C384 workload)" if frac == 1 else f" ({frac:.4f} of the C384 workload)")
+    return (delp, area, fields), pts, desc
+
+
+def time_cpu(sample, nthreads, reps, warm=1):
+    for _ in range(warm):
+        cpu_reference_step(sample, nthreads)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        cpu_reference_step(sample, nthreads)
+    return (time.perf_counter() - t0) / reps
 
 
 def run_reference(args):
+    """The reference arm: the reference's CPU algorithm (oracle port -- the reference stack itself
+    cannot be installed here) over the WHOLE workload of our arm, all six tiles per
+    step, on all host cores; plus the single-thread figure (a reference worker runs dask
+    single-threaded, coarsen_restarts.py:68) on one tile."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -206,21 +253,18 @@ def run_reference(args):
 
     R.lib()
     cores = os.cpu_count() or 1
-    sample, pts, desc = cpu_sample(0)
-    for _ in range(max(args.warmup, 1)):
-        cpu_reference_step(sample, cores)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        cpu_reference_step(sample, cores)
-    dt = (time.perf_counter() - t0) / args.steps
+    sample, pts, desc = cpu_sample(0, ntile=NTILE)
+    dt = time_cpu(sample, cores, args.steps, warm=max(min(args.warmup, 2), 1))
     val = pts / dt
+    one, pts1, desc1 = cpu_sample(0, ntile=1, ny=64)
+    dt1 = time_cpu(one, 1, 1, warm=0)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "C384->C48 pressure-level fv_core A-grid (delp + W,T,ua,va), f=8, kord=1, iv=1, "
-                               "extrapolate=False; each step = bounded sample: " + desc},
+        "config": {"workload": WORKLOAD, "reference_step": "each step = " + desc},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
+        "cpu_baseline_1thread": {"value": pts1 / dt1, "unit": UNIT, "cores": 1, "kind": "port", "sample": desc1},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
         "note": "reference stack (xarray/dask/xgcm + Fortran mappm) cannot run in this image; this is the CPU oracle "
@@ -247,23 +291,19 @@ def bind_to_gpu_numa_node(index):
         pass
 
 
-def run_c3072(args):
+C3072_N1_CACHE = "/tmp/b200cs_c3072_n1.json"           # written by an N=1 run on this box, read by the N>1 runs after it
+C3072_N1_COMMITTED = os.path.join(ROOT, "profiles", "r02_c3072_n1.json")  # the builder's own N=1 measurement
+
+
+def c3072_measure(torch, dist, dev, world, rank, local_rank, steps, warmup, sample_clocks=False):
     """BASELINE configs[4] / SURVEY.md 8d config 5: one C3072 -> C48 timestep (factor 64), delp + 4
     fields, fp32, 6 tiles x 79 levels x 3072 x 3072 = 89.7 GB of input, sharded by (tile, coarse
-    row) over the ranks with no data-path collective (fv3net_b200/shard.py); an asynchronous NCCL
-    all_gather collects the coarse outputs (21.8 MB in total).  Strong scaling: the work is fixed."""
-    import torch
-    import torch.distributed as dist
-
+    row) over the ranks with no data-path collective (fv3net_b200/shard.py; the reference shards
+    the same way per subtile, workflows/dataflow/fv3net/pipelines/coarsen_surface_c3072.py:28-29,
+    87-99); an asynchronous NCCL all_gather collects the coarse outputs (21.8 MB in total).
+    Strong scaling: the work is fixed.  Returns the record on rank 0 (None elsewhere)."""
     from fv3net_b200 import core, shard
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
     n, f, km, nf = 3072, 64, KM, NFIELDS
     ncy = n // f
     ranges = shard.plan(NTILE, ncy, world)
@@ -287,42 +327,48 @@ def run_c3072(args):
         for x in fields[1:]:
             x.normal_(0, 10, generator=g)
         data.append((delp, area, fields))
-    mine = torch.zeros((per, nf + 1, km, n // f), dtype=torch.float32, device=dev)
-    gathered = torch.empty((world * per,) + tuple(mine.shape[1:]), dtype=torch.float32, device=dev) if world > 1 else None
-    pending = [None]
+    # every segment's coarse outputs land, through the kernel's `out`, in their part of ONE flat
+    # buffer of fixed size (the all_gather needs equal sizes on all ranks): no stack / permute /
+    # copy inside the timed step; segment i = [nf + 1, 1, km, rows_i, cx] at its offset
+    cx = n // f
+    flat = torch.zeros(((nf + 1) * km * per * cx,), dtype=torch.float32, device=dev)
+    outbuf, off = [], 0
+    for _, cy0, cy1 in segs:
+        cnt = (nf + 1) * km * (cy1 - cy0) * cx
+        outbuf.append(flat[off:off + cnt].view(nf + 1, 1, km, cy1 - cy0, cx))
+        off += cnt
+    gathered = torch.empty((world,) + tuple(flat.shape), dtype=torch.float32, device=dev) if world > 1 else None
+    pending = []
 
     def step():
-        if pending[0] is not None:
-            pending[0].wait()
-        row = 0
-        for delp, area, fields in data:
-            outs, dco = core.pressure_coarsen(fields, delp, area, f, TOA, mask_mode="phalf", mode=core.FAST)
-            t = torch.stack(list(outs) + [dco])[:, 0].permute(2, 0, 1, 3)  # [rows_c, nf+1, km, cx]
-            mine[row:row + t.shape[0]] = t
-            row += t.shape[0]
+        for h in pending:
+            h.wait()
+        pending.clear()
+        for i, (delp, area, fields) in enumerate(data):
+            core.pressure_coarsen(fields, delp, area, f, TOA, mask_mode="phalf", mode=core.FAST, out=outbuf[i])
         if world > 1:
-            pending[0] = dist.all_gather_into_tensor(gathered, mine, async_op=True)
+            pending.append(dist.all_gather_into_tensor(gathered, flat, async_op=True))
 
     def drain():
-        if pending[0] is not None:
-            pending[0].wait()
-            pending[0] = None
+        for h in pending:
+            h.wait()
+        pending.clear()
 
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(max(warmup, 3)):
         step()
     drain()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     sampler = ClockSampler(local_rank)
-    if rank == 0:
+    if rank == 0 and sample_clocks:
         sampler.start()
         time.sleep(0.3)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
         torch.cuda.synchronize()
-    steps = min(args.steps, 10)
+    steps = max(3, min(steps, 10))
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     for _ in range(steps):
@@ -331,34 +377,163 @@ def run_c3072(args):
     ev1.record()
     torch.cuda.synchronize()
     ms = ev0.elapsed_time(ev1)
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop() if (rank == 0 and sample_clocks) else None
     if world > 1:
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
         dist.barrier()
+    del data, outbuf, gathered, flat
+    torch.cuda.empty_cache()
+    if rank != 0:
+        return None
     ms_per_step = ms / steps
     points = NTILE * km * n * n * nf
     alg = algorithmic_bytes(NTILE, km, n, f, nf)
     peak, peak_src = measured_peak()
+    rec = {
+        "metric": "fine grid pts/s, C3072->C48 pressure-level coarsening (delp + 4 fields, 6 tiles x 79 levels)",
+        "value": points / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": steps,
+        "warmup": max(warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C3072->C48 (factor 64) pressure-level coarsening, delp + 4 fields, 89.7 GB, "
+                               "sharded by (tile, coarse row); wide-window fused kernel (FAST arithmetic)",
+                   "l2": "inputs larger than L2, no flush needed",
+                   "collective": "none" if world == 1 else "NCCL all_gather of the coarse outputs, asynchronous"},
+        "clocks": clocks, "e2e": None, "gpu_launches": steps * len(segs) * 3,
+        "roofline": {"bound": "hbm", "achieved": alg / (ms_per_step * 1e-3) / 1e9 / world, "peak": peak, "unit": "GB/s",
+                     "frac": alg / (ms_per_step * 1e-3) / 1e9 / world / peak, "traffic": None, "peak_source": peak_src,
+                     "kernel": "wba_wide_f32_kernel<64> + pressure_coarsen_sweep_kernel<4,8,WIDE> + wide_finalize_kernel",
+                     "algorithmic_bytes_per_launch": alg, "note": "per-GPU average over the three kernels of a step"},
+        "cpu_baseline": None}
+    # strong-scaling reference: the N=1 time measured on THIS box by an earlier run, else the committed one
+    if world == 1:
+        try:
+            json.dump({"ms_per_step": ms_per_step, "when": time.strftime("%Y-%m-%dT%H:%M:%SZ", time.gmtime())}, open(C3072_N1_CACHE, "w"))
+        except Exception:
+            pass
+        rec["n1_ms_per_step"], rec["n1_source"], rec["speedup_vs_n1"] = ms_per_step, "this run", 1.0
+    else:
+        for path, src in ((C3072_N1_CACHE, "N=1 run on this box (" + C3072_N1_CACHE + ")"),
+                          (C3072_N1_COMMITTED, "builder's N=1 measurement (profiles/r02_c3072_n1.json)")):
+            try:
+                n1 = float(json.load(open(path))["ms_per_step"])
+                rec["n1_ms_per_step"], rec["n1_source"], rec["speedup_vs_n1"] = n1, src, n1 / ms_per_step
+                break
+            except Exception:
+                continue
+    return rec
+
+
+def run_c3072(args):
+    """`--workload c3072`: the C3072 strong-scaling step alone, as the JSON line."""
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    rec = c3072_measure(torch, dist, dev, world, rank, local_rank, args.steps, args.warmup, sample_clocks=True)
     if rank == 0:
-        print(json.dumps({
-            "metric": "fine grid pts/s, C3072->C48 pressure-level coarsening (delp + 4 fields, 6 tiles x 79 levels)",
-            "value": points / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "C3072->C48 (factor 64) pressure-level coarsening, delp + 4 fields, 89.7 GB, "
-                                   "sharded by (tile, coarse row); wide-window fused kernel (FAST arithmetic)",
-                       "l2": "inputs larger than L2, no flush needed",
-                       "collective": "none" if world == 1 else "NCCL all_gather of the coarse outputs, asynchronous"},
-            "clocks": clocks, "e2e": None, "gpu_launches": steps * len(data) * 3,
-            "roofline": {"bound": "hbm", "achieved": alg / (ms_per_step * 1e-3) / 1e9 / world, "peak": peak, "unit": "GB/s",
-                         "frac": alg / (ms_per_step * 1e-3) / 1e9 / world / peak, "traffic": None, "peak_source": peak_src,
-                         "kernel": "wba_wide_f32_kernel<64> + pressure_coarsen_sweep_kernel<4,8,WIDE> + wide_finalize_kernel",
-                         "algorithmic_bytes_per_launch": alg, "note": "per-GPU average over the three kernels of a step"},
-            "cpu_baseline": None}))
+        print(json.dumps(rec))
     if world > 1:
         dist.destroy_process_group()
+
+
+def dropin_measure(torch, core, delp, area, fields, mode, e2e):
+    """The drop-in call as a user of the reference makes it (regridz.py:31-78 + coarsen.py:183-218, fused):
+    labelled arrays wrapping PLAIN numpy (pageable host memory) in, labelled numpy out, through
+    fv3net_b200.cubedsphere.pressure_level_coarsen.  Every step uploads its 1.40 GB and downloads its
+    coarse result; the host copy into pinned staging slabs runs on all cores under the DMA."""
+    from fv3net_b200 import cubedsphere as cs
+    from fv3net_b200.labelled import DataArray, Dataset
+
+    dims = ["tile", "zaxis_1", "yaxis_2", "xaxis_1"]
+    names = ["W", "T", "ua", "va"][:len(fields)]
+    ds = Dataset({k: DataArray(x.cpu().numpy(), dims=dims) for k, x in zip(names, fields)})
+    d = DataArray(delp.cpu().numpy(), dims=dims, name="delp")
+    a = DataArray(area.cpu().numpy(), dims=["tile", "yaxis_2", "xaxis_1"], name="area")
+    checks = []
+
+    def call():
+        out, dco = cs.pressure_level_coarsen(ds, d, a, TOA, FACTOR, mode=mode)
+        checks.append(float(np.asarray(dco.values)[0, 0, 0, 0]) + float(np.asarray(out[names[0]].values)[0, 0, 0, 0]))
+
+    call()
+    torch.cuda.synchronize()
+    n = 3
+    t0 = time.perf_counter()
+    for _ in range(n):
+        call()
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) * 1e3 / n
+    assert len(set(checks)) == 1
+    h2d = sum(int(np.asarray(ds[k].values).nbytes) for k in names) + int(np.asarray(d.values).nbytes) + int(np.asarray(a.values).nbytes)
+    d2h = (len(names) + 1) * NTILE * KM * (NFINE // FACTOR) ** 2 * 4
+    rec = {"value": points_per_step() / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "steps": n,
+           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+           "api": "fv3net_b200.cubedsphere.pressure_level_coarsen(Dataset, delp, area, toa, 8) with numpy-backed labelled arrays "
+                  "(pageable memory) -> numpy-backed Dataset"}
+    if e2e:
+        rec["vs_pinned_pipeline"] = ms / e2e["ms_per_step"]
+    return rec
+
+
+def whole_timestep_measure(torch, core, delp, area, fields, mode, dev):
+    """coarsen_restarts_on_pressure (coarsen_restarts.py:155-240) for ONE C384 timestep resident in HBM:
+    fv_core with A-grid winds (delp, W, T, ua, va on pressure levels; phis, DZ; D-grid u, v on their
+    edge lines; hydrostatic adjustment), 9 tracers on pressure levels, fv_srf_wnd.  Algorithmic
+    bytes as SURVEY.md 8d counts them: every array the recipe needs read once, outputs written once."""
+    from fv3net_b200 import restarts
+
+    n, km, f, nt = NFINE, KM, FACTOR, NTILE
+    g = torch.Generator(device=dev).manual_seed(5)
+    U = lambda lo, hi, *sh: torch.empty(sh, device=dev).uniform_(lo, hi, generator=g)  # noqa: E731
+    N = lambda sd, *sh: torch.empty(sh, device=dev).normal_(0.0, sd, generator=g)  # noqa: E731
+    fv_core = {"phis": U(0, 5e4, nt, n, n), "delp": delp, "DZ": -U(20, 800, nt, km, n, n), "W": fields[1],
+               "T": fields[0], "ua": fields[2], "va": fields[3],
+               "u": N(10, nt, km, n + 1, n), "v": N(10, nt, km, n, n + 1)}
+    tracers = {k: N(1e-3, nt, km, n, n).abs_() for k in ("sphum", "liq_wat", "rainwat", "ice_wat", "snowwat", "graupel",
+                                                         "o3mr", "sgs_tke", "cld_amt")}
+    srf = {"u_srf": N(5, nt, n, n), "v_srf": N(5, nt, n, n)}
+    grid = {"area": area, "dx": U(2.0e4, 2.88e4, nt, n + 1, n), "dy": U(2.0e4, 2.88e4, nt, n, n + 1)}
+    rs = {"fv_core.res": fv_core, "fv_tracer.res": tracers, "fv_srf_wnd.res": srf}
+    E, c = 4, n // f
+    fld, cfl = nt * km * n * n * E, nt * km * c * c * E
+    lines = nt * km * (c + 1) * n * E
+    alg = {"fv_core A-grid (delp, DZ, W, T, ua, va, phis, area)": 6 * fld + 2 * nt * n * n * E + 6 * cfl,
+           "fv_core D-grid u, v (needed lines: wind + 2 delp rows + spacing)": 2 * (3 * lines + nt * (c + 1) * n * E + nt * km * (c + 1) * c * E),
+           "fv_tracer (9 fields + delp, area)": 10 * fld + nt * n * n * E + 9 * cfl,
+           "fv_srf_wnd": 3 * nt * n * n * E}
+    total = sum(alg.values())
+
+    def run():
+        return restarts.coarsen_restarts_on_pressure(f, grid, TOA, rs, coarsen_agrid_winds=True, mode=mode)
+
+    for _ in range(2):
+        run()
+    torch.cuda.synchronize()
+    reps = 7
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
+    ev[0].record()
+    for i in range(reps):
+        run()
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    ts = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(reps))
+    ms = ts[len(ts) // 2]
+    peak, peak_src = measured_peak()
+    del rs, fv_core, tracers, srf, grid
+    torch.cuda.empty_cache()
+    return {"ms": ms, "algorithmic_bytes": total, "bytes_by_part": alg, "achieved_gbs": total / ms / 1e6,
+            "frac": total / ms / 1e6 / peak, "peak_source": peak_src,
+            "fine_points_per_s": (16 * nt * km * n * n + 2 * nt * km * (n + 1) * n) / ms * 1e3,
+            "what": "restarts.coarsen_restarts_on_pressure(8, grid, 300.0, {fv_core, fv_tracer, fv_srf_wnd}, "
+                    "coarsen_agrid_winds=True), device resident, median of 7; mode = the headline's"}
 
 
 def main():
@@ -370,6 +545,12 @@ def main():
     ap.add_argument("--mode", default="fast", choices=["exact", "fast"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the sub-records timed after the headline (other terrains, whole timestep, C3072 strong scaling, "
+                         "drop-in end-to-end): a quick kernel-only line")
+    ap.add_argument("--terrain", default="smooth", choices=["smooth", "orography", "rough"],
+                    help="synthetic surface pressure of the headline workload (see surface_pressure); the other two are "
+                         "timed as `other_terrain`")
     ap.add_argument("--workload", default="c384", choices=["c384", "c3072"],
                     help="c384 (default): BASELINE.json's metric, one C384 timestep per GPU (weak scaling); "
                          "c3072: BASELINE configs[4], ONE C3072 -> C48 timestep (factor 64, delp + 4 fields, 89.7 GB) "
@@ -402,7 +583,7 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     mode = core.EXACT if args.mode == "exact" else core.FAST
 
-    delp, area, fields = synth_device(torch, 1000 + rank, dev)
+    delp, area, fields = synth_device(torch, 1000 + rank, dev, args.terrain)
     cdim = NFINE // FACTOR
     # N > 1: each rank's coarse outputs land in one contiguous buffer (no staging copy) and are
     # all-gathered asynchronously -- the gather of step i runs under the kernel of step i + 1
@@ -430,13 +611,30 @@ def main():
         mine = [torch.empty((NFIELDS + 1, NTILE, KM, cdim, cdim), dtype=torch.float32, device=dev) for _ in range(nbuf)]
         gathered = [torch.empty((world,) + tuple(mine[0].shape), dtype=torch.float32, device=dev) for _ in range(nbuf)] if world > 1 else None
 
+    side = torch.cuda.Stream(device=dev) if use_peer else None
+    bar_done = [None] * nbuf  # event: the barrier that follows the kernel which wrote buffer i has completed
+
     def step():
         i = counter[0] % nbuf
         counter[0] += 1
         if use_peer:
+            # Ordering, with two buffers and the barriers on a SIDE stream (off the kernels' critical path):
+            #   readers of buffer i wait for the barrier after the kernel that wrote it (bar_done[i]);
+            #   the kernel that REUSES buffer i (two steps later) waits for the barrier of the step in
+            #   between, which every peer enters only after it has consumed buffer i (side-stream order).
+            comp = torch.cuda.current_stream()
+            j = (i + 1) % nbuf
+            if bar_done[j] is not None:
+                comp.wait_event(bar_done[j])
             outs, dco = core.pressure_coarsen(fields, delp, area, FACTOR, TOA, mask_mode="phalf", mode=mode, out=local,
                                               peer_ptrs=gath[i].peer_ptrs)
-            gath[i].barrier()  # all writers of buffer i are done: gath[i].buffer holds every rank's outputs
+            wrote = torch.cuda.Event()
+            wrote.record(comp)
+            side.wait_event(wrote)
+            with torch.cuda.stream(side):
+                gath[i].barrier()  # all writers of buffer i are done: gath[i].buffer holds every rank's outputs
+                bar_done[i] = torch.cuda.Event()
+                bar_done[i].record(side)
             return outs, dco
         if world > 1 and pending[i] is not None:
             pending[i].wait()  # the gather that last used this buffer pair
@@ -450,11 +648,21 @@ def main():
             if pending[i] is not None:
                 pending[i].wait()
                 pending[i] = None
+        if use_peer:  # the timed region ends when the last step's outputs are complete on every rank
+            torch.cuda.current_stream().wait_stream(side)
 
     for _ in range(args.warmup):
         step()
     drain()
     torch.cuda.synchronize()
+    slab_err = None
+    if rank == 0 and mode == core.FAST:
+        # once, untimed: the launch that is about to be timed, checked against the CPU oracle on a slab
+        # of this very input (tile 2, two coarse rows): coarse delp bit-identical, fields within 1e-6
+        so, sd = core.pressure_coarsen(fields, delp, area, FACTOR, TOA, mask_mode="phalf", mode=mode)
+        slab_err = check_fast_slab(so, sd, fields, delp, area)
+        assert slab_err <= 1e-6, f"FAST kernel differs from the oracle on the bench slab: {slab_err:.3e} > 1e-6"
+        del so, sd
     if use_peer:  # once, untimed: the peer-written buffer equals an NCCL all_gather of the same outputs
         ref = torch.empty((world,) + tuple(local.shape), dtype=torch.float32, device=dev)
         dist.all_gather_into_tensor(ref, local)
@@ -506,6 +714,26 @@ def main():
     ms_per_step = ms / args.steps
     value = world * points_per_step() / (ms_per_step * 1e-3)
 
+    # ---- data dependence: the same launch on the other two surface-pressure fields ----------
+    other_terrain = None
+    if rank == 0 and not args.no_extras:
+        other_terrain = {}
+        for name in ("smooth", "orography", "rough"):
+            if name == args.terrain:
+                continue
+            g2 = torch.Generator(device=dev).manual_seed(77)
+            d2 = synth_delp(torch, surface_pressure(torch, name, g2, dev), g2, dev)
+            for _ in range(2):
+                core.pressure_coarsen(fields, d2, area, FACTOR, TOA, mask_mode="phalf", mode=mode)
+            t0_, t1_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0_.record()
+            for _ in range(5):
+                core.pressure_coarsen(fields, d2, area, FACTOR, TOA, mask_mode="phalf", mode=mode)
+            t1_.record()
+            torch.cuda.synchronize()
+            other_terrain[name] = {"kernel_ms": t0_.elapsed_time(t1_) / 5, "vs_headline": t0_.elapsed_time(t1_) / 5 / kernel_ms}
+            del d2
+
     # ---- end to end through the public API from pinned host buffers -------------------------
     e2e = None
     if not args.no_e2e:
@@ -547,6 +775,26 @@ def main():
                "d2h_bytes_per_step": d2h, "ms_per_step": e_ms, "steps": n_e2e}
         del h_delp, h_area, h_fields
 
+    # ---- the drop-in call as a user makes it: plain (pageable) numpy in, numpy out ------------
+    e2e_dropin = None
+    if world == 1 and not args.no_e2e and not args.no_extras:
+        e2e_dropin = dropin_measure(torch, core, delp, area, fields, mode, e2e)
+
+    # ---- one whole restart timestep, device resident ----------------------------------------
+    whole = None
+    if world == 1 and not args.no_extras:
+        whole = whole_timestep_measure(torch, core, delp, area, fields, mode, dev)
+
+    # ---- C3072 -> C48 strong scaling (BASELINE configs[4]), same process, after the headline --
+    c3072 = None
+    if not args.no_extras and mode == core.FAST:
+        del delp, area, fields
+        torch.cuda.empty_cache()
+        try:
+            c3072 = c3072_measure(torch, dist, dev, world, rank, local_rank, 5, 3)
+        except torch.cuda.OutOfMemoryError as e:  # 89.7 GB / world per rank
+            c3072 = {"unavailable": f"out of memory: {str(e)[:120]}"} if rank == 0 else None
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -566,17 +814,23 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "C384->C48 pressure-level fv_core A-grid (delp + W,T,ua,va): 6 tiles x 79 levels x "
-                               "384 x 384 fp32, f=8, kord=1, iv=1, extrapolate=False, fused kernel",
-                   "arithmetic_mode": args.mode, "l2": "inputs (1.42 GB) larger than L2, no flush needed",
-                   "per_rank": "one synthetic timestep per GPU (weak)", "collective": ("none" if world == 1 else "fused: the coarsening kernel stores its coarse outputs (21.8 MB/rank) into every rank's gather buffer over NVLink peer memory, one device-side barrier per step" if use_peer else "NCCL all_gather of the coarse outputs (21.8 MB/rank), asynchronous: overlaps the next step")},
+        "config": {"workload": WORKLOAD, "kernel": "one fused launch per step",
+                   "arithmetic_mode": args.mode, "terrain": args.terrain, "l2": "inputs (1.42 GB) larger than L2, no flush needed",
+                   "per_rank": "one synthetic timestep per GPU (weak)", "collective": ("none" if world == 1 else "fused: the coarsening kernel stores its coarse outputs (21.8 MB/rank) into every rank's gather buffer over NVLink peer memory, one device-side barrier per step on a side stream (two buffers)" if use_peer else "NCCL all_gather of the coarse outputs (21.8 MB/rank), asynchronous: overlaps the next step")},
         "clocks": clocks,
         "other_mode": {"arithmetic_mode": "exact" if args.mode == "fast" else "fast", "kernel_ms": other_ms},
+        "parity_slab": None if slab_err is None else {
+            "max_rel_err": slab_err, "bound": 1e-6, "what": "FAST outputs of this very launch vs the CPU oracle on tile 2, coarse "
+            "rows 8-9, all levels and fields; relative to sum|w x|/sum w per coarse cell; coarse delp bit-identical"},
+        "other_terrain": other_terrain,
+        "whole_timestep": whole,
+        "c3072_strong": c3072,
+        "e2e_dropin": e2e_dropin,
         "e2e": e2e,
         "gpu_launches": args.steps,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "peak_source": peak_src,
-                     "kernel": ("pressure_coarsen_sweep_kernel<NF=4,FY=8>" if args.mode == "fast"
+                     "kernel": ("pressure_coarsen_tma_kernel<NP=2,NFL=4> (TMA tile ring, packed f32x2 PPM)" if args.mode == "fast"
                                 else "pressure_coarsen_kernel<EXACT,NF=4,f32,f32,FX=8>"),
                      "algorithmic_bytes_per_launch": abytes, "kernel_ms": kernel_ms},
     }
@@ -586,13 +840,12 @@ def main():
         R.lib()
         cores = os.cpu_count() or 1
         sample, pts, desc = cpu_sample(0)
-        cpu_reference_step(sample, cores)
-        t0 = time.perf_counter()
-        reps = 3
-        for _ in range(reps):
-            cpu_reference_step(sample, cores)
-        dt = (time.perf_counter() - t0) / reps
+        dt = time_cpu(sample, cores, 3)
         line["cpu_baseline"] = {"value": pts / dt, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
+        # what ONE reference worker does (dask single-threaded, coarsen_restarts.py:68): BASELINE.md 3 (i)
+        one, pts1, desc1 = cpu_sample(0, ntile=1, ny=64)
+        dt1 = time_cpu(one, 1, 1, warm=0)
+        line["cpu_baseline_1thread"] = {"value": pts1 / dt1, "unit": UNIT, "cores": 1, "kind": "port", "sample": desc1}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

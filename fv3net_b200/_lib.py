@@ -27,6 +27,7 @@ EXPORTS = [
     "b200cs_dominant_mask", "b200cs_pressure_at_midpoint_log", "b200cs_exposed_area_weights",
     "b200cs_pressure_coarsen_gather", "b200cs_pressure_coarsen_gather_workspace_bytes",
     "b200cs_pressure_coarsen_wide", "b200cs_pressure_coarsen_wide_workspace_bytes", "b200cs_mappm_fast",
+    "b200cs_host_copy",
 ]
 
 _lib = None
@@ -84,6 +85,7 @@ def load():
     lib.b200cs_dominant_mask.argtypes = [vp, vp, i32, i64, i64, i64, i32, dbl, dbl, vp, vp, vp]
     lib.b200cs_pressure_at_midpoint_log.argtypes = [vp, vp, i32, i64, i32, i64, dbl, vp]
     lib.b200cs_exposed_area_weights.argtypes = [vp, vp, i32, vp, i32, vp, i64, i32, i64, i64, i32, vp]
+    lib.b200cs_host_copy.argtypes = [vp, vp, i64, i32]
     lib.b200cs_hydrostatic_balance.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i64, i32, i64, dbl, dbl, dbl, dbl, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)

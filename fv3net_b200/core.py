@@ -10,6 +10,7 @@ Every function launches hand-written sm_100a kernels through the C ABI of ``libb
 Reference citations are relative to /root/reference/external/vcm/vcm/.
 """
 import ctypes
+import os
 
 import numpy as np
 import torch
@@ -218,9 +219,7 @@ def block_upsample(obj, upsampling_factor, axes=(-2, -1), staggered=None):
     axes = tuple(a % nd for a in axes)
     if not set(axes) <= {nd - 2, nd - 1}:
         raise ValueError("block_upsample works on the last two axes")
-    if o.element_size() not in (4, 8):
-        o = o.to(torch.float64)
-    o = o.contiguous()
+    o = o.contiguous()  # any 1/2/4/8-byte dtype keeps its type: the kernel only moves bits
     cy, cx = o.shape[-2:]
     fy = f if (nd - 2) in axes else 1
     fx = f if (nd - 1) in axes else 1
@@ -462,11 +461,16 @@ def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.
     wdt = w.dtype
     cdt = _promote(d, w)
     if f not in (2, 4, 8):  # a coarse cell wider than one CTA tile (C3072 -> C48 is factor 64)
-        if edge_lines or peer_ptrs or out is not None:
+        if edge_lines or peer_ptrs:
             raise ValueError("pressure_coarsen: edge lines / gather buffers need a factor of 2, 4 or 8")
         all_f32 = fdt == torch.float32 and d.dtype == torch.float32 and wdt == torch.float32
-        if mode == FAST and all_f32 and f in (16, 32, 64) and int(kord) <= 3 and fs:
-            outs, dco = _pressure_coarsen_wide(fs, d, w, f, toa_pressure, mask_mode, iv, kord, return_delp_coarse)
+        wide = mode == FAST and all_f32 and f in (16, 32, 64) and int(kord) <= 3 and bool(fs)
+        if out is not None and (not wide or tuple(out.shape) != (len(fs) + 1, nb0, km, cy, cx) or out.dtype != torch.float32
+                                or not out.is_contiguous() or out.device != d.device):
+            raise ValueError("pressure_coarsen: out= with a factor above 8 needs the FAST fp32 wide kernel and a "
+                             "contiguous [nfields + 1, B, km, cy, cx] float32 device tensor")
+        if wide:
+            outs, dco = _pressure_coarsen_wide(fs, d, w, f, toa_pressure, mask_mode, iv, kord, return_delp_coarse, out)
         else:
             outs, dco = _pressure_coarsen_unfused(fs, d, w, f, toa_pressure, mask_mode, iv, kord,
                                                   FAST if (mode == FAST and int(kord) <= 3) else EXACT)
@@ -500,15 +504,25 @@ def pressure_coarsen(fields, delp, weights, coarsening_factor, toa_pressure=300.
     return outs, dco
 
 
-def _pressure_coarsen_wide(fs, d, w, f, toa_pressure, mask_mode, iv, kord, return_delp_coarse):
+_WIDE_WS = {}  # (device index, stream) -> workspace tensor, grown on demand
+
+
+def _pressure_coarsen_wide(fs, d, w, f, toa_pressure, mask_mode, iv, kord, return_delp_coarse, out=None):
     """b200cs_pressure_coarsen_wide: FAST arithmetic, fp32, factor 16 / 32 / 64."""
     nb0, km, ny, nx = d.shape
     cy, cx = ny // f, nx // f
     lib = _lib.load()
-    outs = [torch.empty((nb0, km, cy, cx), dtype=torch.float32, device=d.device) for _ in fs]
-    dco = torch.empty((nb0, km, cy, cx), dtype=torch.float32, device=d.device) if return_delp_coarse else None
+    if out is not None:
+        outs, dco = [out[i] for i in range(len(fs))], out[len(fs)]
+    else:
+        outs = [torch.empty((nb0, km, cy, cx), dtype=torch.float32, device=d.device) for _ in fs]
+        dco = torch.empty((nb0, km, cy, cx), dtype=torch.float32, device=d.device) if return_delp_coarse else None
     nws = lib.b200cs_pressure_coarsen_wide_workspace_bytes(nb0, km, ny, nx, f)
-    ws = torch.empty(max(nws, 4), dtype=torch.uint8, device=d.device)
+    # the workspace is scratch between the three launches of one call: one per (device, stream), reused
+    key = (d.device.index, _stream())
+    ws = _WIDE_WS.get(key)
+    if ws is None or ws.numel() < nws:
+        ws = _WIDE_WS[key] = torch.empty(max(nws, 4), dtype=torch.uint8, device=d.device)
     rc = lib.b200cs_pressure_coarsen_wide(
         len(fs), _lib.ptrarr([x.data_ptr() for x in fs]), _lib.i64arr(fs[0].stride()[:3]), d.data_ptr(),
         _lib.i64arr(d.stride()[:3]), w.data_ptr(), _lib.i64arr(w.stride()[:2]), _lib.ptrarr([o.data_ptr() for o in outs]),
@@ -546,33 +560,90 @@ def _pressure_coarsen_unfused(fs, d, w, f, toa_pressure, mask_mode, iv, kord, re
 
 
 _COPY_STREAMS = {}
+_STAGING = {}  # device index -> _PinnedRing
+
+
+class _PinnedRing:
+    """Reused pinned staging slabs for host-resident (pageable) inputs.  cudaMemcpyAsync from
+    pageable memory is a synchronous staged copy on one host thread; here every array slab is
+    copied into a pinned slot by all host cores (b200cs_host_copy) and leaves the slot by DMA, so
+    the host copy of slab i+1 overlaps the DMA of slab i and the kernels of the previous tile."""
+
+    NSLOT = 4
+
+    def __init__(self, dev):
+        self.dev, self.bytes, self.slots, self.free = dev, 0, [], []
+        self.next = 0
+        self.nthreads = max(1, min(32, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)))
+
+    def _grow(self, nbytes):
+        if nbytes <= self.bytes:
+            return
+        for ev in self.free:
+            if ev is not None:
+                ev.synchronize()
+        self.bytes = int(nbytes)
+        self.slots = [torch.empty(self.bytes, dtype=torch.uint8).pin_memory() for _ in range(self.NSLOT)]
+        self.free = [None] * self.NSLOT
+
+    def upload(self, src, dst, stream):
+        """src: C-contiguous host tensor (pageable or pinned); dst: device tensor of the same dtype
+        and element count; the DMA is queued on ``stream``.  Returns once the host copy is done."""
+        nbytes = src.numel() * src.element_size()
+        if src.is_pinned():
+            with torch.cuda.stream(stream):
+                dst.copy_(src.view_as(dst), non_blocking=True)
+            return
+        self._grow(nbytes)
+        i = self.next
+        self.next = (i + 1) % self.NSLOT
+        if self.free[i] is not None:
+            self.free[i].synchronize()  # the DMA that last read this slot has finished
+        slot = self.slots[i]
+        _lib.check(_lib.load().b200cs_host_copy(slot.data_ptr(), src.data_ptr(), nbytes, self.nthreads), "host_copy")
+        with torch.cuda.stream(stream):
+            dst.view(-1).view(torch.uint8).copy_(slot[:nbytes], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(stream)
+        self.free[i] = ev
 
 
 def _pressure_coarsen_from_host(fields, delp, weights, f, toa_pressure, mask_mode, edge_lines, iv, kord, mode,
                                 return_delp_coarse, seq_window, was_np):
-    """Host-resident inputs: the upload dominates (1.4 GB over PCIe vs ~1 ms of kernel at C384), so
-    tiles are uploaded on a copy stream while the previous tile is coarsened (the per-tile loop of
-    the reference's recipes, turned into a two-stage pipeline)."""
+    """Host-resident inputs -- what the drop-in signatures receive: plain numpy arrays
+    (regridz.py:31-78).  The upload dominates (1.4 GB over PCIe against < 1 ms of kernel at C384),
+    so it is a three-stage pipeline per tile (the per-tile loop of the reference's recipes):
+    all-core host copy into pinned slabs (_PinnedRing) | DMA on a copy stream | fused kernel."""
     dev = device()
     comp = torch.cuda.current_stream()
     key = dev.index
     if key not in _COPY_STREAMS:
         _COPY_STREAMS[key] = torch.cuda.Stream(device=dev)
-    copy = _COPY_STREAMS[key]
-    as_t = lambda a: a if isinstance(a, torch.Tensor) else torch.as_tensor(np.asarray(a))  # noqa: E731
+        _STAGING[key] = _PinnedRing(dev)
+    copy, ring = _COPY_STREAMS[key], _STAGING[key]
+
+    def as_t(a):
+        t = a if isinstance(a, torch.Tensor) else torch.as_tensor(np.asarray(a))
+        if t.dtype not in _DT:
+            t = t.to(torch.float64)
+        return t
+
     hd, hw, hf = as_t(delp), as_t(weights), [as_t(x) for x in fields]
     nb = hd.shape[0]
     outs_t, dco_t = [], []
     copy.wait_stream(comp)
-    staged = []
     for t in range(nb):
-        with torch.cuda.stream(copy):
-            dt = [x[t:t + 1].to(dev, non_blocking=True) for x in [hd, hw] + hf]
-            ev = torch.cuda.Event()
-            ev.record(copy)
-        staged.append((dt, ev))
-    for t in range(nb):
-        dt, ev = staged[t]
+        dt = []
+        for x in [hd, hw] + hf:
+            src = x[t:t + 1]
+            if not src.is_contiguous():
+                src = src.contiguous()
+            with torch.cuda.stream(copy):  # owned by the copy stream's pool; record_stream below covers the kernels
+                dst = torch.empty(src.shape, dtype=src.dtype, device=dev)
+            ring.upload(src, dst, copy)
+            dt.append(dst)
+        ev = torch.cuda.Event()
+        ev.record(copy)
         comp.wait_event(ev)
         for x in dt:
             x.record_stream(comp)
@@ -581,7 +652,6 @@ def _pressure_coarsen_from_host(fields, delp, weights, f, toa_pressure, mask_mod
                                  seq_window=seq_window)
         outs_t.append(o)
         dco_t.append(dc)
-        staged[t] = None
     outs = [torch.cat([o[i] for o in outs_t]) for i in range(len(hf))]
     dco = torch.cat(dco_t) if return_delp_coarse else None
     if was_np:

@@ -648,7 +648,6 @@ extern "C" int b200cs_weighted_block_average(const void* obj, int obj_dtype, con
         const bool w3d = sw[1] != 0;
         // levels per thread: 1 keeps the grid at several waves at C384 (13,824 cells x 79 levels); the
         // 2-D weights are re-read from L2
-        static const int lv_env = [] { const char* e = getenv("B200CS_WBA_LV"); return e ? atoi(e) : 1; }();
         dim3 grid((unsigned)((ncell + 127) / 128), 1, 1);
 #define B200CS_WBA8(LVV, W3, H2)                                                                     \
     grid.y = (unsigned)((nb1 + LVV - 1) / LVV);                                                      \
@@ -659,8 +658,6 @@ extern "C" int b200cs_weighted_block_average(const void* obj, int obj_dtype, con
                                                        nb0, nb1, cy, cx)
         if (w2) { if (w3d) { B200CS_WBA8(2, true, true); } else { B200CS_WBA8(2, false, true); } }
         else if (w3d) { B200CS_WBA8(2, true, false); }
-        else if (lv_env == 4) { B200CS_WBA8(4, false, false); }
-        else if (lv_env == 2) { B200CS_WBA8(2, false, false); }
         else { B200CS_WBA8(1, false, false); }
 #undef B200CS_WBA8
         return check_launch("weighted_block_average(8x8 f32)");
@@ -727,14 +724,15 @@ extern "C" int b200cs_block_upsample(const void* in, void* out, int elem_size, i
                                      void* stream) {
     B200CS_REQUIRE(in && out, "block_upsample: NULL argument");
     B200CS_REQUIRE(fy >= 1 && fx >= 1 && cy >= 1 && cx >= 1, "block_upsample: bad extents");
-    B200CS_REQUIRE(elem_size == 4 || elem_size == 8, "block_upsample: elem_size must be 4 or 8");
+    B200CS_REQUIRE(elem_size == 1 || elem_size == 2 || elem_size == 4 || elem_size == 8,
+                   "block_upsample: elem_size must be 1, 2, 4 or 8");
     const int64_t ny = y_staggered ? (cy - 1) * fy + 1 : cy * fy;
     const int64_t nx = x_staggered ? (cx - 1) * fx + 1 : cx * fx;
     const int64_t total = nb * ny * nx;
     if (total == 0) return B200CS_OK;
     cudaStream_t st = as_stream(stream);
     const int vec = 16 / elem_size;
-    if (!y_staggered && !x_staggered && fx % vec == 0 && ((uintptr_t)out & 15) == 0) {
+    if (elem_size >= 4 && !y_staggered && !x_staggered && fx % vec == 0 && ((uintptr_t)out & 15) == 0) {
         const int64_t rows = nb * cy;
         const unsigned g = (unsigned)(rows < (1 << 30) ? rows : (1 << 30));
         if (elem_size == 4)
@@ -743,7 +741,11 @@ extern "C" int b200cs_block_upsample(const void* in, void* out, int elem_size, i
             upsample_rows_kernel<uint64_t, 2><<<g, 128, 0, st>>>((const uint64_t*)in, (uint64_t*)out, rows, cx, nx, fy, fx);
         return check_launch("block_upsample");
     }
-    if (elem_size == 4)
+    if (elem_size == 1)  // masks (bool / int8) and 2-byte dtypes keep their width: the op only moves bits
+        upsample_kernel<uint8_t><<<(unsigned)(nb * ny < (1 << 30) ? nb * ny : (1 << 30)), 128, 0, st>>>((const uint8_t*)in, (uint8_t*)out, nb, cy, cx, ny, nx, fy, fx);
+    else if (elem_size == 2)
+        upsample_kernel<uint16_t><<<(unsigned)(nb * ny < (1 << 30) ? nb * ny : (1 << 30)), 128, 0, st>>>((const uint16_t*)in, (uint16_t*)out, nb, cy, cx, ny, nx, fy, fx);
+    else if (elem_size == 4)
         upsample_kernel<uint32_t><<<(unsigned)(nb * ny < (1 << 30) ? nb * ny : (1 << 30)), 128, 0, st>>>((const uint32_t*)in, (uint32_t*)out, nb, cy, cx, ny, nx, fy, fx);
     else
         upsample_kernel<uint64_t><<<(unsigned)(nb * ny < (1 << 30) ? nb * ny : (1 << 30)), 128, 0, st>>>((const uint64_t*)in, (uint64_t*)out, nb, cy, cx, ny, nx, fy, fx);

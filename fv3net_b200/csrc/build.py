@@ -28,6 +28,7 @@ UNITS = [("status", "status.cu", ["-fmad=false"]),
          ("column_ops", "column_ops.cu", ["-fmad=false"]),
          ("elementwise", "elementwise.cu", ["-fmad=false"]),
          ("pc_api", "pressure_coarsen_api.cu", ["-fmad=false"]),
+         ("host_stage", "host_stage.cu", ["-fmad=false"]),
          ("pc_fast", "pressure_coarsen_fast.cu", ["-fmad=true"])]
 for fx in (2, 4, 8):
     UNITS.append((f"pc_fx{fx}_m0", "pressure_coarsen_inst.cu", ["-fmad=false", f"-DB200CS_FX={fx}", "-DB200CS_MODE=0"]))
@@ -69,7 +70,7 @@ def build(verbose=False, force=False):
             rebuilt |= did
     objs = [os.path.join(OBJ, u[0] + ".o") for u in UNITS]
     if rebuilt or _stale(OUT, objs):
-        cmd = [NVCC] + ARCH + ["-shared", "-ccbin", HOSTCXX, "-o", OUT] + objs + ["-lcudart"]
+        cmd = [NVCC] + ARCH + ["-shared", "-ccbin", HOSTCXX, "-o", OUT] + objs + ["-lcudart", "-lpthread"]
         p = subprocess.run(cmd, capture_output=True, text=True)
         if p.returncode != 0:
             raise RuntimeError(f"link failed:\n{p.stdout}\n{p.stderr}")

@@ -60,13 +60,8 @@ static int pc_dispatch(int nfields, const void* const* fields, int field_dtype, 
         if (mode != B200CS_FAST || !pc_fast_covers(a, field_dtype, p_dtype, w_dtype) || fy != fx)
             return set_err(B200CS_EUNSUPPORTED, "pressure_coarsen_gather: only the FAST fp32 8x8 kernel (kord <= 3) scatters to peers");
     }
-    // with no fields the kernel still produces delp_coarse: run it on a dummy 1-field launch
-    const void* dummy_in[1] = {delp};
-    void* dummy_out[1] = {nullptr};
-    if (nfields == 0) {
+    if (nfields == 0)
         return set_err(B200CS_EINVAL, "pressure_coarsen: nfields == 0 (use b200cs_weighted_block_average for delp)");
-    }
-    (void)dummy_in; (void)dummy_out;
     if (mode == B200CS_EXACT) {
         if (fx == 8) return pc_entry_fx8_m0(a, p_dtype, w_dtype);
         if (fx == 4) return pc_entry_fx4_m0(a, p_dtype, w_dtype);

@@ -10,17 +10,11 @@ namespace b200cs {
 bool pc_fast_covers(const PcArgs& a, int field_dtype, int p_dtype, int w_dtype) {
     return pc_fast_eligible(a, field_dtype, p_dtype, w_dtype);
 }
-// B200CS_FAST_KERNEL=v1 selects the first (output-layer-major) fast kernel, kept for A/B profiling
-static bool use_v1() {
-    static const bool v = [] { const char* e = getenv("B200CS_FAST_KERNEL"); return e && e[0] == 'v' && e[1] == '1'; }();
-    return v;
-}
 int pc_fast_entry(const PcArgs& a) {
-    if (use_v1() && a.npeer == 0) return a.fy == 8 ? launch_pc_fast_fields<8>(a) : launch_pc_fast_fields<1>(a);
-    static const int tma_ctas = [] { const char* e = getenv("B200CS_TMA_CTAS"); return e ? atoi(e) : 3; }();  // dev switch: 0 = sweep kernel
+    static const int tma_ctas = [] { const char* e = getenv("B200CS_TMA_CTAS"); return e ? atoi(e) : 2; }();  // dev switch: 0 = sweep kernel
     if (tma_ctas > 0 && pc_tma_eligible(a)) {
         // TMA-fed kernel; -1: the arrays cannot be described to TMA (alignment, strides) -> sweep kernel
-        const int rc = tma_ctas == 2 ? launch_pc_tma_fields<2>(a) : launch_pc_tma_fields<3>(a);
+        const int rc = tma_ctas == 3 ? launch_pc_tma_fields<3>(a) : launch_pc_tma_fields<2>(a);
         if (rc != -1) return rc;
     }
     if (a.fy == 8) return launch_pc_sweep_fields<8>(a);

@@ -11,14 +11,14 @@
 //   * Every level of every array reaches shared memory as ONE 2-D TMA tile (cp.async.bulk.tensor,
 //     8 rows x 32 columns = 1 KB, 128-byte swizzle) issued by a single lane; completion is an
 //     mbarrier transaction count.  The per-thread LDGSTS, their 64-bit pointer arithmetic and the
-//     cp.async group bookkeeping are gone.  A slot of the 4-level ring is refilled by the LAST warp
+//     cp.async group bookkeeping are gone.  A slot of the 8-level ring is refilled by the LAST warp
 //     that releases it (shared-memory counter), so nobody ever waits for a free slot.
 //   * A warp owns HALF A COARSE CELL: 8 rows x 4 columns (one 16-byte chunk per row, which the
 //     128-byte swizzle spreads over all banks), two warps per cell.  All 32 lanes share the
 //     cell's level table (uniform loads) and the weighted values of an output level are summed
 //     over 32 lanes, not 8: accumulators shrink from [8 rows][km][4][NF+1] to [8 warps][km][NF+1]
-//     (50 KB -> 12.6 KB), which with 80 registers per thread admits 3 CTAs per SM.  Neighbouring
-//     columns of a compact 8 x 4 patch also sit on closer output levels than a 32-column strip.
+//     (50 KB -> 12.6 KB), which pays for the deeper level ring.  Neighbouring columns of a
+//     compact 8 x 4 patch also sit on closer output levels than a 32-column strip.
 //   * The column machine works on PAIRS of fields with packed fp32 instructions and a clamp-form
 //     limiter (ppm_pack.cuh).
 //   * Phase A reads delp from TMA tiles too (8 levels per tile); one thread per (level, cell) forms
@@ -34,7 +34,7 @@
 
 namespace b200cs {
 
-constexpr int kTmaSlots = 4;          // level ring depth
+constexpr int kTmaSlots = 8;          // level ring depth: two halves of 4 slots (the layer loop is unrolled by 4)
 constexpr int kTmaTile = 1024;        // bytes of one array-level tile (8 rows x 128 B)
 constexpr int kTmaKA = 8;             // Phase A: levels per delp tile
 constexpr int kTmaMaxArrays = 5;      // 4 fields + delp
@@ -67,17 +67,20 @@ __device__ __forceinline__ void tma_load4(unsigned dst, const CUtensorMap* map, 
         ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(z), "r"(b), "r"(bar) : "memory");
 }
 
-// shared memory carve-up (bytes from the 1 KB-aligned base); fixed-size parts first so that the ring,
-// the barriers and the counters sit at compile-time offsets
+// shared memory carve-up (bytes from the 1 KB-aligned base); fixed-size parts first.  The level ring
+// is two HALVES of 4 slots; a half holds its tiles, its four "full" barriers and its four release
+// counters at the same offsets, so that ONE register (0 or kHalf) selects the half for all three.
 template <int NA>
 struct TmaSmem {
-    static constexpr int ring = 0;                                      // [4][NA] tiles
-    static constexpr int stage = ring + kTmaSlots * NA * kTmaTile;      // float4 [kStage][256]; Phase A: 4 delp tiles of 8 KB
+    static constexpr int half = 4 * NA * kTmaTile + 1024;               // tiles of 4 slots, then barriers / counters
+    static constexpr int hbar = 4 * NA * kTmaTile;                      // u64 full[4] of the half
+    static constexpr int hcnt = hbar + 32;                              // unsigned released[4] of the half
+    static constexpr int ring = 0;
+    static constexpr int stage = ring + 2 * half;                       // float4 [kStage][256]; Phase A: 4 delp tiles of 8 KB
     static constexpr int w = stage + kStage * kThreads * 16;            // float [8][32] weights (NaN -> 0)
     static constexpr int den = w + kTileY * kTileX * 4;                 // float [4] cell weight sums
-    static constexpr int cnt = den + 16;                                // unsigned [4] releases seen per slot
-    static constexpr int bar = cnt + 16;                                // u64 full[4], fullA[4]
-    static constexpr int lvl = bar + 64;                                // float4 [4][LS] level tables; then float acc[8][km][NV]
+    static constexpr int bar_a = den + 16;                              // u64 fullA[4] (Phase A tiles)
+    static constexpr int lvl = bar_a + 32;                              // float4 [4][LS] level tables; then float acc[8][km][NV]
 };
 
 // keeps a cheap-to-recompute value in its register (ptxas rematerialises address arithmetic inside the hot loop)
@@ -101,29 +104,34 @@ __device__ __forceinline__ float lds32(unsigned a) {
 }
 __device__ __forceinline__ void sts32(unsigned a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
 
-// The level ring: slot s = level % 4 holds NA tiles (fields, then delp).
+// The level ring: level j lives in slot j % 4 of half (j / 4) % 2 and holds NA tiles (fields, then
+// delp); its barrier completes with phase parity (j / 8) % 2.  A slot is refilled, with level j + 8,
+// by the LAST warp that releases it (shared-memory counter): nobody ever waits for a free slot, and
+// up to 7 levels (35 KB at NA = 5) are in flight per CTA -- the sweep of one level takes a warp a
+// few hundred cycles, DRAM latency under load is a few thousand.
 template <int NA>
 struct TmaRing {
     unsigned sb;          // shared address of the carve-up's base
     unsigned nact;        // warps that consume the ring
-    __device__ __forceinline__ unsigned full(int slot) const { return sb + TmaSmem<NA>::bar + slot * 8; }
-    __device__ __forceinline__ unsigned tile(int slot, int i) const { return sb + TmaSmem<NA>::ring + (slot * NA + i) * kTmaTile; }
-    __device__ __forceinline__ void issue(const TmaMaps& maps, int slot, int level) const {
-        const unsigned bar = full(slot);
+    // hoff = 0 or TmaSmem<NA>::half
+    __device__ __forceinline__ unsigned full(unsigned hoff, int slot) const { return sb + hoff + TmaSmem<NA>::hbar + slot * 8; }
+    __device__ __forceinline__ void issue(const TmaMaps& maps, unsigned hoff, int slot, int level) const {
+        const unsigned bar = full(hoff, slot);
         mbar_expect_tx(bar, NA * kTmaTile);
 #pragma unroll
         for (int i = 0; i < NA; i++)
-            tma_load4(tile(slot, i), &maps.lvl[i], (int)(blockIdx.x * kTileX), (int)(blockIdx.y * kTileY), level, (int)blockIdx.z, bar);
+            tma_load4(sb + hoff + (slot * NA + i) * kTmaTile, &maps.lvl[i], (int)(blockIdx.x * kTileX), (int)(blockIdx.y * kTileY),
+                      level, (int)blockIdx.z, bar);
     }
-    // every lane of the warp has read its values of `level` from `slot`: the last warp to say so
-    // refills the slot with level + 4
-    // (the warp is converged at the shared loads, which therefore precede lane 0's atomic)
-    __device__ __forceinline__ void release(const TmaMaps& maps, int slot, int level, int km, int lane) const {
+    // every lane of the warp has read its values of `level` from (hoff, slot): the last warp to say
+    // so refills the slot with level + 8.  (The warp is converged at the shared loads, which
+    // therefore precede lane 0's atomic.)
+    __device__ __forceinline__ void release(const TmaMaps& maps, unsigned hoff, int slot, int level, int km, int lane) const {
         if (lane == 0) {
             unsigned old;
-            asm volatile("atom.shared.inc.u32 %0, [%1], %2;" : "=r"(old) : "r"(sb + TmaSmem<NA>::cnt + slot * 4), "r"(nact - 1) : "memory");
+            asm volatile("atom.shared.inc.u32 %0, [%1], %2;" : "=r"(old) : "r"(sb + hoff + TmaSmem<NA>::hcnt + slot * 4), "r"(nact - 1) : "memory");
             if (old == nact - 1) {
-                if (level + kTmaSlots < km) issue(maps, slot, level + kTmaSlots);
+                if (level + kTmaSlots < km) issue(maps, hoff, slot, level + kTmaSlots);
             }
         }
     }
@@ -139,8 +147,8 @@ struct TmaCtx {
     int k;                // next output level of this lane
     int kdone;            // (warp-uniform) output levels below this one are reduced
     int nanwin;           // > 0: a NaN level is inside this column's stencil, literal limiter tests
-    unsigned par;         // phase parity of ring slot 0 for the next level that lands there
-    unsigned accw;        // shared address this lane adds to when a level is reduced (its field's / the weight's slot of level kdone)
+    unsigned hoff;        // half of the ring the next levels are read from (0 or TmaSmem::half)
+    unsigned par;         // phase parity of that half's barriers
     float pt, pb, rdpc, thr;
     float wv, whalf, psurf, psmin;
     int km, lane;
@@ -214,34 +222,110 @@ __device__ __forceinline__ float4 unpack4(const f2 (&o)[NP]) {
     return make_float4(f2_lo(o[0]), f2_hi(o[0]), 0.f, 0.f);
 }
 
-// Reduces the staged levels every lane of the warp has passed: [c.kdone, min over lanes of k).
-// Lanes 0, 8, 16, 24 (NP = 2; 0 and 16 for NP = 1) end up with a field total, lane 1 adds the weight sum.
+// sums the four values (a.lo, a.hi, b.lo, b.hi) over the 8 lanes that share lane >> 3, transposing:
+// lanes 2f and 2f + 1 of the group end up with the total of value f (NP = 1: two values, lanes
+// 0..3 hold the first, 4..7 the second)
 template <int NP>
-__device__ __forceinline__ void tma_reduce(TmaCtx<NP>& c) {
+__device__ __forceinline__ float reduce_fields8t(f2 a, f2 b, int lane) {
+    const unsigned m = 0xffffffffu;
+    float t;
+    if (NP == 2) {
+        const bool hi = lane & 4;
+        f2 keep = hi ? b : a;
+        const f2 send = hi ? a : b;
+        f2 recv = send;
+#if defined(__CUDA_ARCH__)
+        recv.v = __shfl_xor_sync(m, send.v, 4);
+#endif
+        keep = f2_add(keep, recv);
+        const bool b1 = lane & 2;
+        const float k0 = b1 ? f2_hi(keep) : f2_lo(keep), s0 = b1 ? f2_lo(keep) : f2_hi(keep);
+        t = k0 + __shfl_xor_sync(m, s0, 2);
+    } else {
+        const bool hi = lane & 4;
+        const float k0 = hi ? f2_hi(a) : f2_lo(a), s0 = hi ? f2_lo(a) : f2_hi(a);
+        t = k0 + __shfl_xor_sync(m, s0, 4);
+        t = t + __shfl_xor_sync(m, t, 2);
+    }
+    return t + __shfl_xor_sync(m, t, 1);
+}
+
+// Reduces `nlev` (1..4, warp-uniform) staged levels starting at c.kdone, all of which every lane of
+// the warp has passed.  The 8 lanes with lane >> 3 == i take level kdone + i: each reads the
+// staged float4 of four source lanes (sub, sub + 8, sub + 16, sub + 24: 8 reducer lanes cover 128
+// contiguous bytes per load, conflict-free), adds them with packed adds, and a 3-step transposing
+// butterfly finishes the sum -- 4 LDS.128 + 4 STS.128 + ~25 arithmetic / shuffle instructions
+// for four levels, where one butterfly over 32 lanes per level took 45 per level.
+template <int NP>
+__device__ __forceinline__ void tma_reduce_batch(TmaCtx<NP>& c, int nlev) {
     const unsigned full = 0xffffffffu;
     constexpr int NV = 2 * NP + 1;
-    const int kend = (int)__reduce_min_sync(full, (unsigned)c.k);
-    const bool writer = (c.lane == 1) || (NP == 2 ? ((c.lane & 7) == 0) : ((c.lane & 15) == 0));
-    for (int kk = c.kdone; kk < kend; kk++) {
-        const unsigned slot_p = c.buf + (kk & (kStage - 1)) * (kThreads * 16);
-        float4 pv = lds128(slot_p);
+    const int i = c.lane >> 3, sub = c.lane & 7;
+    const int kk = c.kdone + i;
+    const bool on = i < nlev;
+    const unsigned base = (c.buf - c.lane * 16) + (kk & (kStage - 1)) * (kThreads * 16) + sub * 16;
+    __syncwarp();  // the staged values were written by other lanes
+    float4 v[4];
+#pragma unroll
+    for (int t = 0; t < 4; t++) v[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (on) {
+#pragma unroll
+        for (int t = 0; t < 4; t++) v[t] = lds128(base + t * 128);
         // a slot that holds no pending level reads as zero: a lane that overflowed the ring at
-        // level kk went through tma_accumulate_slow and must not be counted again
-        sts128(slot_p, make_float4(0.f, 0.f, 0.f, 0.f));
-        float tot = reduce_fields32<NP>(pv, c.lane);
-        if (__any_sync(full, tot != tot)) {  // NaN-skipping sums (xarray's coarsen().sum()): rare
-            pv.x = nan_to_zero(pv.x); pv.y = nan_to_zero(pv.y); pv.z = nan_to_zero(pv.z); pv.w = nan_to_zero(pv.w);
-            tot = reduce_fields32<NP>(pv, c.lane);
-        }
-        // the mask threshold of the level is the same for the 32 lanes; c.psmin = their smallest
-        // surface pressure: uniform test, no vote
-        const float thr = lds32(c.lvl + kk * 16 + 8);
-        float rd = c.whalf;
-        if (!(thr < c.psmin)) rd = reduce_all32(thr < c.psurf ? nan_to_zero(c.wv) : 0.f);
-        if (writer) sts32(c.accw, lds32(c.accw) + (c.lane == 1 ? rd : tot));
-        c.accw += NV * 4;
+        // a level went through tma_accumulate_slow and must not be counted again
+#pragma unroll
+        for (int t = 0; t < 4; t++) sts128(base + t * 128, make_float4(0.f, 0.f, 0.f, 0.f));
     }
-    c.kdone = kend > c.kdone ? kend : c.kdone;
+    f2 a = f2_add(f2_add(f2_make(v[0].x, v[0].y), f2_make(v[1].x, v[1].y)), f2_add(f2_make(v[2].x, v[2].y), f2_make(v[3].x, v[3].y)));
+    f2 b = f2_make(0.f, 0.f);
+    if (NP == 2) b = f2_add(f2_add(f2_make(v[0].z, v[0].w), f2_make(v[1].z, v[1].w)), f2_add(f2_make(v[2].z, v[2].w), f2_make(v[3].z, v[3].w)));
+    float tot = reduce_fields8t<NP>(a, b, c.lane);
+    if (__any_sync(full, tot != tot)) {  // NaN-skipping sums (xarray's coarsen().sum()): rare
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+            v[t].x = nan_to_zero(v[t].x); v[t].y = nan_to_zero(v[t].y); v[t].z = nan_to_zero(v[t].z); v[t].w = nan_to_zero(v[t].w);
+        }
+        a = f2_add(f2_add(f2_make(v[0].x, v[0].y), f2_make(v[1].x, v[1].y)), f2_add(f2_make(v[2].x, v[2].y), f2_make(v[3].x, v[3].y)));
+        if (NP == 2) b = f2_add(f2_add(f2_make(v[0].z, v[0].w), f2_make(v[1].z, v[1].w)), f2_add(f2_make(v[2].z, v[2].w), f2_make(v[3].z, v[3].w)));
+        tot = reduce_fields8t<NP>(a, b, c.lane);
+    }
+    // weight sum of the level: every lane of the warp is above the mask threshold (c.psmin = the
+    // smallest surface pressure of the 32 columns) except near the surface
+    const float thr = on ? lds32(c.lvl + kk * 16 + 8) : -INFINITY;
+    float rd = c.whalf;
+    if (__any_sync(full, !(thr < c.psmin))) {
+        for (int ii = 0; ii < nlev; ii++) {
+            const float thr_i = __shfl_sync(full, thr, ii * 8);
+            const float r = reduce_all32(thr_i < c.psurf ? nan_to_zero(c.wv) : 0.f);
+            rd = (i == ii) ? r : rd;
+        }
+    }
+    if (on) {
+        const unsigned dst = c.acc + kk * (NV * 4);
+        const int f = NP == 2 ? (sub >> 1) : (sub >> 2);
+        if (sub == 1) sts32(dst + 2 * NP * 4, rd);  // a level is reduced once; tma_accumulate_slow adds values only
+        else if (NP == 2 ? ((sub & 1) == 0) : ((sub & 3) == 0)) sts32(dst + f * 4, lds32(dst + f * 4) + tot);
+    }
+    __syncwarp();  // the zeros are in place before any lane stages into these slots again
+    c.kdone += nlev;
+}
+
+// Reduces the staged levels every lane of the warp has passed, [c.kdone, min over lanes of k), four
+// at a time; fewer only when a lane is about to overflow its staging ring (steep terrain inside the
+// warp's patch) or at the end of the column (FLUSH).
+template <int NP, bool FLUSH>
+__device__ __forceinline__ void tma_reduce(TmaCtx<NP>& c) {
+    const unsigned full = 0xffffffffu;
+    const int kend = (int)__reduce_min_sync(full, (unsigned)c.k);
+    int n = kend - c.kdone;
+    if (!FLUSH && n < 4) {
+        if (n <= 0) return;
+        if ((int)__reduce_max_sync(full, (unsigned)c.k) - c.kdone < kStage - 1) return;
+    }
+    while (n > 0) {
+        tma_reduce_batch<NP>(c, n < 4 ? n : 4);
+        n -= 4;
+    }
 }
 
 // output edges inside the current source layer (all remaining ones when it is the last layer):
@@ -271,7 +355,7 @@ __device__ __forceinline__ void tma_emit(TmaCtx<NP>& c) {
         }
     }
     if (!LAST) c.m.close(c.pt);
-    tma_reduce<NP>(c);
+    tma_reduce<NP, LAST>(c);
 }
 
 // this thread's values of one level: NFL fields (an odd count repeats the last one) and delp
@@ -293,13 +377,16 @@ template <int NP, int NFL, int PH>
 __device__ __forceinline__ void tma_enter(TmaCtx<NP>& c, const TmaRing<NFL + 1>& rg, const TmaMaps& maps, unsigned src0, int L) {
     f2 qn[NP];
     if (L >= 2) {
-        // level L+2 lives in slot (PH+2)&3; slot 0 starts a new round of the ring
+        // level L+2 lives in slot (PH+2)&3 of the current half; slot 0 starts the next half
         constexpr int slot = (PH + 2) & 3;
-        if (slot == 0) c.par ^= 1u;
+        if (slot == 0) {
+            c.par ^= (c.hoff != 0);  // a new round of the ring begins when half 0 comes up again
+            c.hoff = TmaSmem<NFL + 1>::half - c.hoff;
+        }
         float d;
-        mbar_wait(rg.full(slot), c.par);
-        tma_read<NP, NFL>(src0 + slot * (NFL + 1) * kTmaTile, qn, d);
-        rg.release(maps, slot, L + 2, c.km, c.lane);
+        mbar_wait(rg.full(c.hoff, slot), c.par);
+        tma_read<NP, NFL>(src0 + c.hoff + slot * (NFL + 1) * kTmaTile, qn, d);
+        rg.release(maps, c.hoff, slot, L + 2, c.km, c.lane);
         c.pacc = c.pacc + nan_to_zero(d);
         f2 s2 = qn[0];
         if (NP == 2) s2 = f2_add(s2, qn[NP - 1]);
@@ -385,7 +472,7 @@ pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL>
     float* s_acc = reinterpret_cast<float*>(s_lvl + (size_t)CW * LS);         // [8 warps][km][NV]
     float* s_w = reinterpret_cast<float*>(smem_raw + SM::w);                  // [8][32]
     float* s_den = reinterpret_cast<float*>(smem_raw + SM::den);              // [CW]
-    const unsigned bar_a = sbase + SM::bar + kTmaSlots * 8;
+    const unsigned bar_a = sbase + SM::bar_a;
 
     TmaRing<NA> rg;
     rg.sb = sbase;
@@ -396,12 +483,16 @@ pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL>
     const int nchunk = (km + kTmaKA - 1) / kTmaKA;
     if (tid == 0) {
 #pragma unroll
-        for (int i = 0; i < 2 * kTmaSlots; i++) mbar_init(sbase + SM::bar + i * 8, 1);
-#pragma unroll
-        for (int i = 0; i < kTmaSlots; i++) sts32(sbase + SM::cnt + i * 4, 0.f);
+        for (int i = 0; i < 4; i++) {
+            mbar_init(rg.full(0, i), 1);
+            mbar_init(rg.full(SM::half, i), 1);
+            mbar_init(bar_a + i * 8, 1);
+            sts32(sbase + SM::hcnt + i * 4, 0.f);
+            sts32(sbase + SM::half + SM::hcnt + i * 4, 0.f);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        // Phase A's first four delp tiles, then levels 0..3 of the ring
+        // Phase A's first four delp tiles, then levels 0..7 of the ring
 #pragma unroll
         for (int cch = 0; cch < 4; cch++) {
             if (cch < nchunk) {
@@ -411,7 +502,8 @@ pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL>
             }
         }
 #pragma unroll
-        for (int j = 0; j < kTmaSlots; j++) rg.issue(maps, j, j);  // km >= 4
+        for (int j = 0; j < kTmaSlots; j++)
+            if (j < km) rg.issue(maps, j < 4 ? 0u : (unsigned)SM::half, j & 3, j);
     }
     for (int t = tid; t < 8 * km * NV; t += kThreads) s_acc[t] = 0.f;
 
@@ -525,17 +617,17 @@ pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL>
         c.acc = sbase + SM::lvl + CW * LS * 16 + wid * km * NV * 4;
         c.buf = sbase + SM::stage + tid * 16;
         c.par = 0;
+        c.hoff = 0;  // levels 0..3 (init) come from half 0; level 4 flips to half 1
         c.psmin = -reduce_max32(-pacc);
-        c.accw = c.acc + (lane == 1 ? 2 * NP : (NP == 2 ? (lane >> 3) : (lane >> 4))) * 4;
         const unsigned src0 = opaque(sbase + SM::ring + my_off);
         float4 v0;  // weighted level-0 values
         {
             f2 qA[NP], qB[NP], qC[NP], qD[NP];
             float d0, d1, d2, d3, p[5];
-            mbar_wait(rg.full(0), 0); tma_read<NP, NFL>(src0 + 0 * NA * kTmaTile, qA, d0); rg.release(maps, 0, 0, km, lane);
-            mbar_wait(rg.full(1), 0); tma_read<NP, NFL>(src0 + 1 * NA * kTmaTile, qB, d1); rg.release(maps, 1, 1, km, lane);
-            mbar_wait(rg.full(2), 0); tma_read<NP, NFL>(src0 + 2 * NA * kTmaTile, qC, d2); rg.release(maps, 2, 2, km, lane);
-            mbar_wait(rg.full(3), 0); tma_read<NP, NFL>(src0 + 3 * NA * kTmaTile, qD, d3); rg.release(maps, 3, 3, km, lane);
+            mbar_wait(rg.full(0, 0), 0); tma_read<NP, NFL>(src0 + 0 * NA * kTmaTile, qA, d0); rg.release(maps, 0, 0, 0, km, lane);
+            mbar_wait(rg.full(0, 1), 0); tma_read<NP, NFL>(src0 + 1 * NA * kTmaTile, qB, d1); rg.release(maps, 0, 1, 1, km, lane);
+            mbar_wait(rg.full(0, 2), 0); tma_read<NP, NFL>(src0 + 2 * NA * kTmaTile, qC, d2); rg.release(maps, 0, 2, 2, km, lane);
+            mbar_wait(rg.full(0, 3), 0); tma_read<NP, NFL>(src0 + 3 * NA * kTmaTile, qD, d3); rg.release(maps, 0, 3, 3, km, lane);
             p[0] = toa;
             p[1] = p[0] + nan_to_zero(d0);
             p[2] = p[1] + nan_to_zero(d1);

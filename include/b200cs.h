@@ -117,7 +117,8 @@ int b200cs_block_reduce(const void* obj, int dtype, const int64_t obj_stride[2],
  * Block upsample.  Replaces block_upsample / block_upsample_like
  * (VCM/cubedsphere/coarsen.py:843-938, VCM/xarray_utils.py:37-82): each element repeated f
  * times along y and x; a staggered (interface) axis repeats all but its last element.
- * in contiguous [nb, cy, cx] -> out contiguous [nb, ny, nx]; elem_size 4 or 8 bytes.
+ * in contiguous [nb, cy, cx] -> out contiguous [nb, ny, nx]; elem_size 1, 2, 4 or 8 bytes (bits are
+ * moved, never converted: a bool mask stays a bool mask).
  */
 int b200cs_block_upsample(const void* in, void* out, int elem_size, int64_t nb, int64_t cy,
                           int64_t cx, int fy, int fx, int y_staggered, int x_staggered,
@@ -340,6 +341,15 @@ int b200cs_compare_scalar(int cmp, const void* a, int dtype, double scalar, doub
 int b200cs_dominant_mask(const void* fine, const void* coarse, int dtype, int64_t nb, int64_t ny,
                          int64_t nx, int factor, double rtol, double atol,
                          const uint8_t* and_mask, uint8_t* out, void* stream);
+
+/*
+ * Host-side staging for the drop-in entry points, which receive plain (pageable) numpy arrays
+ * (VCM/cubedsphere/regridz.py:31-78, coarsen.py:183-218): copies `bytes` from src to dst with up to
+ * `nthreads` host threads.  dst is a pinned staging buffer the caller then hands to
+ * cudaMemcpyAsync; the copy of slab i+1 overlaps the DMA of slab i (fv3net_b200/core.py).
+ * No CUDA call is made.
+ */
+int b200cs_host_copy(void* dst, const void* src, int64_t bytes, int nthreads);
 
 #ifdef __cplusplus
 }

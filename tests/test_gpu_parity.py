@@ -192,6 +192,13 @@ def test_block_upsample(core, oracle):
         for dt in (np.float32, np.float64):
             a = rng.normal(size=shp).astype(dt)
             assert eq(core.block_upsample(a, 8), oracle.block_upsample(a, 8))
+    # 1- and 2-byte dtypes (masks, int16 categories, half floats) keep their dtype, as np.repeat does
+    for dt in (np.bool_, np.int8, np.uint8, np.int16, np.float16):
+        for shp in [(2, 3, 6, 6), (2, 3, 7, 6)]:
+            a = (rng.integers(0, 2, size=shp) if dt is np.bool_ else rng.integers(-100, 100, size=shp)).astype(dt)
+            got = core.block_upsample(a, 4)
+            assert got.dtype == a.dtype
+            assert np.array_equal(got, oracle.block_upsample(a, 4))
     # round trip with the block average (config 4: edge average -> upsample_like)
     u = rng.normal(size=(6, 3, 49, 48)).astype(np.float32)
     dx = rng.uniform(0.5, 1, size=(6, 1, 49, 48)).astype(np.float32)
