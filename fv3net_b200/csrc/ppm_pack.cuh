@@ -25,7 +25,15 @@
 //     incoming level values): the reference's NaN pattern next to a NaN level follows from
 //     those tests being false on NaN and from Fortran MIN/MAX dropping NaN operands (a layer
 //     whose neighbour is NaN can come out FLAT and finite), which no clamp reproduces;
-//   * the parabola is stored as (A6/3, -B): edge() is fma + mul + fma + sub + mul per pair.
+//   * the parabola is stored as its two edge values and their limited deviations from the mean
+//     (AL, AR, dl = AL-q, dr = AR-q), and every piece of an output layer is integrated ANCHORED at
+//     the end of the source layer it touches: from the layer top, I(s) = h (AL - s(1+t) dl - s t dr),
+//     h = p - pe_lo, s = h/dp, t = 1-s; up to the layer bottom, J(t) = g (AR - t(1+s) dr - s t dl),
+//     g = pe_hi - p.  A sliver at either end of a layer whose profile runs into zero there (cloud
+//     water next to a cloud-free layer) keeps the relative accuracy of its own small value; the
+//     "layer mean minus deviation integral" form of the first two designs cancelled there
+//     (tests/test_gpu_parity.py::test_pressure_coarsen_fast_tracer_decades: 4e-3 of the coarse
+//     cell's value).  edge() is 2 fma + fma + 2 mul per pair, close() 2 fma + fma.
 //
 // The functions compile for the host (f2 = two floats) so that tests/harness/ppm_pack_host.cpp
 // runs the same machine on the CPU against the oracle.
@@ -65,6 +73,15 @@ B200CS_HD float xor_sign(float a, float s) {
 #endif
 }
 
+// a with the inverted sign bit of s xor-ed in (-a * sign(s) for s != 0)
+B200CS_HD float xor_nsign(float a, float s) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(__float_as_uint(a) ^ (~__float_as_uint(s) & 0x80000000u));
+#else
+    return signbit(s) ? a : -a;
+#endif
+}
+
 template <int NP>
 struct PpmPack {
     static constexpr int NF = 2 * NP;
@@ -72,15 +89,17 @@ struct PpmPack {
     float PE[4], DP[4];
     f2 E[2][NP], DC[2][NP];
     f2 DQ[2][NP];           // slot j%2: q[j+1] - q[j]
-    f2 a63[NP], nbb[NP];    // limited parabola of the current layer: A6/3 and -B, B = (A6+AR-AL)/2
-    f2 R[NP];               // running mass of the output layer being filled
-    f2 qc[NP];              // q[L] of the current layer
+    f2 AL[NP], AR[NP];      // limited edge values of the current layer
+    f2 DL[NP], DR[NP];      // ... minus the layer mean
+    f2 R[NP];               // mass of the output layer being filled: what lies above the current source layer
+                            // (no edge in this layer yet), else minus I(s) of the last edge
     float r12;              // 1/(dp[L+1]+dp[L+2]) formed by the previous step
     float rdp0;             // 1/dp[L]
     float pe_lo, pe_hi;     // pe[L], pe[L+1]
 
     // boundary layers: ppm_limiters lmt=0 with the Fortran's tests kept literally
-    // (PpmSweep::make_parabola), one pair
+    // (mappm.f90:875-894), one pair.  In deviations: "A6 = 3(AL-q), AR = AL-A6" is dr = -2 dl,
+    // "A6 = 3(AR-q), AL = AR-A6" is dl = -2 dr.
     B200CS_HD void parabola_general(int p, f2 l, f2 r, f2 a1, f2 dm) {
         float a[2], b[2];
         const float lv[2] = {f2_lo(l), f2_hi(l)}, rv[2] = {f2_lo(r), f2_hi(r)};
@@ -92,31 +111,31 @@ struct PpmPack {
             const float ta = (3.f * sm) * df;
             const bool lim = fabsf(ta) > df * df;
             const bool neg = ta > 0.f;
-            const float x = neg ? dl : dr;
-            const float aa = lim ? x : -sm;
-            const float bb = lim ? (neg ? 0.f : 3.f * x) : (-2.f * dl - dr);
+            const float dl2 = lim ? (neg ? dl : -2.f * dr) : dl;
+            const float dr2 = lim ? (neg ? -2.f * dl : dr) : dr;
             const bool flat = (dv[j] == 0.f);
-            a[j] = flat ? 0.f : aa;
-            b[j] = flat ? 0.f : -bb;
+            a[j] = flat ? 0.f : dl2;
+            b[j] = flat ? 0.f : dr2;
         }
-        a63[p] = f2_make(a[0], a[1]);
-        nbb[p] = f2_make(b[0], b[1]);
+        DL[p] = f2_make(a[0], a[1]);
+        DR[p] = f2_make(b[0], b[1]);
+        AL[p] = f2_add(a1, DL[p]);
+        AR[p] = f2_add(a1, DR[p]);
     }
 
     // interior layers: the limiter as two clamps (header)
     B200CS_HD void parabola_interior(int p, f2 l, f2 r, f2 a1, f2 dm) {
         const f2 dl = f2_sub(l, a1), dr = f2_sub(r, a1);
-        const f2 tl = f2_add(dl, dl), tr = f2_add(dr, dr);
+        const f2 tl2 = f2_add(dl, dl), tr2 = f2_add(dr, dr);
         const f2 X = f2_mul(dm, f2_bc(1.2676506e30f));  // 2^100: 0 when dm == 0, else beyond any |dl|
-        const float ml0 = min3abs(f2_lo(dl), f2_lo(tr), f2_lo(X));
-        const float ml1 = min3abs(f2_hi(dl), f2_hi(tr), f2_hi(X));
-        const float mr0 = min3abs(f2_lo(dr), f2_lo(tl), f2_lo(X));
-        const float mr1 = min3abs(f2_hi(dr), f2_hi(tl), f2_hi(X));
-        const f2 ml = f2_make(ml0, ml1), mr = f2_make(mr0, mr1);
-        const f2 e = f2_sub(ml, mr);                       // s * A6/3
-        const f2 g = f2_fma(f2_bc(-2.f), ml, mr);          // s * (-B)
-        a63[p] = f2_make(xor_sign(f2_lo(e), f2_lo(dr)), xor_sign(f2_hi(e), f2_hi(dr)));
-        nbb[p] = f2_make(xor_sign(f2_lo(g), f2_lo(dr)), xor_sign(f2_hi(g), f2_hi(dr)));
+        const float ml0 = min3abs(f2_lo(dl), f2_lo(tr2), f2_lo(X));
+        const float ml1 = min3abs(f2_hi(dl), f2_hi(tr2), f2_hi(X));
+        const float mr0 = min3abs(f2_lo(dr), f2_lo(tl2), f2_lo(X));
+        const float mr1 = min3abs(f2_hi(dr), f2_hi(tl2), f2_hi(X));
+        DL[p] = f2_make(xor_nsign(ml0, f2_lo(dr)), xor_nsign(ml1, f2_hi(dr)));  // -s min(|dl|, 2|dr|)
+        DR[p] = f2_make(xor_sign(mr0, f2_lo(dr)), xor_sign(mr1, f2_hi(dr)));    //  s min(|dr|, 2|dl|)
+        AL[p] = f2_add(a1, DL[p]);
+        AR[p] = f2_add(a1, DR[p]);
     }
 
     // Layer 0.  p[0..4] = pe[0..4]; qA..qD = q[0..3] as NF scalars (km >= 4).  mappm.f90:689-725.
@@ -165,7 +184,6 @@ struct PpmPack {
             DQ[1][j] = f2_sub(Q[2][j], Q[1][j]);
             DQ[0][j] = f2_sub(Q[1][j], Q[0][j]);
             R[j] = f2_bc(0.f);
-            qc[j] = Q[0][j];
             parabola_general(j, f2_make(x1v[a], x1v[b]), E[1][j], Q[0][j], f2_make(dc0v[a], dc0v[b]));
         }
         PE[0] = p[0]; PE[1] = p[1]; PE[2] = p[2]; PE[3] = p[3];
@@ -182,6 +200,13 @@ struct PpmPack {
     // a NaN level (header); uniform across the warp.
     template <int PH>
     B200CS_HD void step(float pn, const f2 (&qn)[NP], bool general) {
+#pragma unroll
+        for (int p = 0; p < NP; p++) Q[(PH + 2) & 3][p] = qn[p];
+        step_inplace<PH>(pn, general);
+    }
+    // ... with q[L+2] already in Q[(PH+2)%4] (the kernel loads it there one step ahead)
+    template <int PH>
+    B200CS_HD void step_inplace(float pn, bool general) {
         constexpr int i0 = PH, i1 = (PH + 1) & 3, i2 = (PH + 2) & 3, i3 = (PH + 3) & 3;
         constexpr int e0 = PH & 1, e1 = (PH + 1) & 1;
         const float dpm = DP[i3], dp0 = DP[i0], dp1 = DP[i1];
@@ -206,9 +231,8 @@ struct PpmPack {
         const float nG3 = -(g * dp0 * a1);
 #pragma unroll
         for (int p = 0; p < NP; p++) {
-            Q[i2][p] = qn[p];
             const f2 q0 = Q[i0][p], q1 = Q[i1][p];
-            const f2 d01 = DQ[e0][p], d12 = f2_sub(qn[p], q1);
+            const f2 d01 = DQ[e0][p], d12 = f2_sub(Q[i2][p], q1);
             DQ[e1][p] = d12;
             const f2 df2 = f2_fma(f2_bc(A), d12, f2_mul(f2_bc(B), d01));
             float dcv[2];
@@ -225,7 +249,6 @@ struct PpmPack {
             const f2 en = f2_fma(f2_bc(nG3), dcn, f2_fma(f2_bc(G2), dm, f2_fma(f2_bc(G1), d01, q0)));
             if (general) parabola_general(p, E[e0][p], en, q0, dm);
             else parabola_interior(p, E[e0][p], en, q0, dm);
-            qc[p] = q0;
             E[e1][p] = en;
             DC[e1][p] = dcn;
         }
@@ -301,7 +324,6 @@ struct PpmPack {
             }
             const f2 l2 = f2_make(lv[0], lv[1]);
             parabola_general(p, E[e0][p], l2, Q[i0][p], DC[e0][p]);
-            qc[p] = Q[i0][p];
             E[e1][p] = l2;
             DC[e1][p] = f2_make(dcv[0], dcv[1]);
             E[e0][p] = f2_make(rv[0], rv[1]);  // interface km has the parity of interface km-2
@@ -316,53 +338,74 @@ struct PpmPack {
         pe_lo = PE[i0]; pe_hi = PE[i1];
         rdp0 = fast_rcp(DP[i0]);
 #pragma unroll
-        for (int p = 0; p < NP; p++) {
-            parabola_general(p, E[e0][p], E[e1][p], Q[i0][p], DC[e0][p]);
-            qc[p] = Q[i0][p];
-        }
+        for (int p = 0; p < NP; p++) parabola_general(p, E[e0][p], E[e1][p], Q[i0][p], DC[e0][p]);
     }
 
     // Output edge pb inside the current layer (pb <= pe_hi), or below the surface when the current
     // layer is the last one: closes the output layer [pt, pb] and opens the next.  scale =
-    // 1/(pb-pt) (times whatever weight the caller folds in).  mappm.f90:76-120 in the mean +
-    // deviation form of ppm_fast.cuh.
+    // 1/(pb-pt) (times whatever weight the caller folds in).  mappm.f90:76-120 with every piece
+    // anchored at the layer end it touches (header).  `on` = false: evaluate, change nothing (the
+    // lanes of a warp that have no edge in this layer run along).
     template <bool LAST = true>
-    B200CS_HD void edge(float pt, float pb, float scale, f2 (&out)[NP]) {
-        const float d = pb - fmaxf(pt, pe_lo);
+    B200CS_HD void edge(float pt, float pb, float scale, f2 (&out)[NP], bool on = true, const f2* qm = nullptr) {
         const float h = (LAST ? fminf(pb, pe_hi) : pb) - pe_lo;
-        const float s = h * rdp0;
-        const float u = 1.f + s;
-        const bool inside = !LAST || pb <= pe_hi;
-        const float nc = h * s - h;  // -dp*s*(1-s)
+        const float g = LAST ? fmaxf(pe_hi - pb, 0.f) : pe_hi - pb;
+        const float s = h * rdp0, t = g * rdp0;
+        const float c2 = s * t, c1 = s + c2;
+        // below the surface the last layer's mean carries on (:118-123); a last layer that lies
+        // entirely inside the output layer enters through its mean (:99-104), whatever its edge values
+        const float ext = LAST ? fmaxf(pb - fmaxf(pt, pe_hi), 0.f) : 0.f;
+        const bool whole = LAST && !(pt > pe_lo) && pb > pe_hi;
+        const bool below = LAST && !(pt < pe_hi);  // output layer entirely below the surface: q[km-1] whatever lies above (:52-54)
 #pragma unroll
         for (int p = 0; p < NP; p++) {
-            const f2 t = f2_fma(a63[p], f2_bc(u), nbb[p]);
-            f2 nD = f2_mul(f2_bc(nc), t);
-            if (LAST && !inside) nD = f2_bc(0.f);
-            out[p] = f2_mul(f2_sub(f2_fma(f2_bc(d), qc[p], R[p]), nD), f2_bc(scale));
-            R[p] = nD;
+            f2 P = f2_fma(f2_bc(-c2), DR[p], f2_fma(f2_bc(-c1), DL[p], AL[p]));
+            if (LAST) P = whole ? qm[p] : P;
+            f2 m = f2_fma(f2_bc(h), P, R[p]);
+            if (LAST) m = below ? f2_mul(f2_bc(ext), qm[p]) : f2_fma(f2_bc(ext), qm[p], m);
+            out[p] = f2_mul(m, f2_bc(scale));
+            const f2 nI = f2_mul(f2_bc(-h), P);
+            if (on) R[p] = nI;
         }
     }
 
-    // Leaving the current layer: what lies below the last output edge pt enters through the mean
-    // (:99-104).  Nothing is added while the level search is still above pt (:70-74).
+    // Leaving the current layer: what lies below its last output edge pt (the whole layer when pt
+    // is not inside it, :99-104) opens the mass of the output layer being filled.  An edge AT
+    // pe_lo belongs to the layer above (edges are emitted while pb <= pe_hi).
     B200CS_HD void close(float pt) {
-        if (pt < pe_hi) {
-            const float d = pe_hi - fmaxf(pt, pe_lo);
+        const float g = pe_hi - fmaxf(pt, pe_lo);
+        const float t = g * rdp0, sv = 1.f - t;
+        const float e2 = sv * t, e1 = t + e2;
+        const float keep = (pt > pe_lo) ? 0.f : 1.f;
 #pragma unroll
-            for (int p = 0; p < NP; p++) R[p] = f2_fma(f2_bc(d), qc[p], R[p]);
+        for (int p = 0; p < NP; p++) {
+            const f2 P = f2_fma(f2_bc(-e2), DL[p], f2_fma(f2_bc(-e1), DR[p], AR[p]));
+            R[p] = f2_fma(f2_bc(g), P, f2_mul(f2_bc(keep), R[p]));
+        }
+    }
+    // ... for layers whose edge values may be NaN (a NaN level inside the stencil): a layer without
+    // an output edge enters through its mean q, as in the reference, and after an edge the mass
+    // above it is dropped, not multiplied by zero
+    B200CS_HD void close_general(float pt, const f2 (&q)[NP]) {
+        const float g = pe_hi - fmaxf(pt, pe_lo);
+        const float t = g * rdp0, sv = 1.f - t;
+        const float e2 = sv * t, e1 = t + e2;
+        const bool whole = !(pt > pe_lo);
+#pragma unroll
+        for (int p = 0; p < NP; p++) {
+            const f2 P = f2_fma(f2_bc(-e2), DL[p], f2_fma(f2_bc(-e1), DR[p], AR[p]));
+            R[p] = whole ? f2_fma(f2_bc(g), q[p], R[p]) : f2_mul(f2_bc(g), P);
         }
     }
 
-    // First output edge p when it does not coincide with pe[0] (general grids).  Call once p <= pe_hi.
+    // First output edge p when it does not coincide with pe[0] (general grids).  Call once p <= pe_hi
+    // (or in the last layer).  An edge above the column leaves the state as it is.
     B200CS_HD void open_edge(float p) {
-        const float h = fminf(fmaxf(p, pe_lo), pe_hi) - pe_lo;
-        const float s = h * rdp0;
-        const float nc = h * s - h;
-        const float u = 1.f + s;
-        const bool inside = (p > pe_lo) && (p <= pe_hi);
+        if (!(p > pe_lo)) return;
+        f2 dummy[NP], qz[NP];
 #pragma unroll
-        for (int j = 0; j < NP; j++) R[j] = inside ? f2_mul(f2_bc(nc), f2_fma(a63[j], f2_bc(u), nbb[j])) : f2_bc(0.f);
+        for (int j = 0; j < NP; j++) qz[j] = f2_sub(AL[j], DL[j]);
+        edge<true>(p, p, 0.f, dummy, true, qz);  // below the surface (last layer): the mass of the whole layer, taken off again by the next edge
     }
 };
 

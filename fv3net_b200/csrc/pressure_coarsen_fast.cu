@@ -1,7 +1,5 @@
 // pressure_coarsen_fast.cu -- instantiations of the specialised FAST fused kernel
 // (pressure_coarsen_fast.cuh).  Built with FMA contraction on (-fmad=true).
-#include <stdlib.h>
-
 #include "pressure_coarsen_fast.cuh"
 #include "pressure_coarsen_sweep.cuh"
 #include "pressure_coarsen_tma.cuh"
@@ -11,10 +9,9 @@ bool pc_fast_covers(const PcArgs& a, int field_dtype, int p_dtype, int w_dtype) 
     return pc_fast_eligible(a, field_dtype, p_dtype, w_dtype);
 }
 int pc_fast_entry(const PcArgs& a) {
-    static const int tma_ctas = [] { const char* e = getenv("B200CS_TMA_CTAS"); return e ? atoi(e) : 2; }();  // dev switch: 0 = sweep kernel
-    if (tma_ctas > 0 && pc_tma_eligible(a)) {
+    if (pc_tma_eligible(a)) {
         // TMA-fed kernel; -1: the arrays cannot be described to TMA (alignment, strides) -> sweep kernel
-        const int rc = tma_ctas == 3 ? launch_pc_tma_fields<3>(a) : launch_pc_tma_fields<2>(a);
+        const int rc = launch_pc_tma_fields(a);
         if (rc != -1) return rc;
     }
     if (a.fy == 8) return launch_pc_sweep_fields<8>(a);

@@ -146,7 +146,7 @@ struct TmaCtx {
     unsigned buf;         // shared address of this thread's staging ring: float4 [kStage] (stride kThreads)
     int k;                // next output level of this lane
     int kdone;            // (warp-uniform) output levels below this one are reduced
-    int nanwin;           // > 0: a NaN level is inside this column's stencil, literal limiter tests
+    int nanwin;           // (warp-uniform) > 0: a NaN level is inside the stencil of some lane, literal limiter tests
     unsigned hoff;        // half of the ring the next levels are read from (0 or TmaSmem::half)
     unsigned par;         // phase parity of that half's barriers
     float pt, pb, rdpc, thr;
@@ -256,14 +256,22 @@ __device__ __forceinline__ float reduce_fields8t(f2 a, f2 b, int lane) {
 // contiguous bytes per load, conflict-free), adds them with packed adds, and a 3-step transposing
 // butterfly finishes the sum -- 4 LDS.128 + 4 STS.128 + ~25 arithmetic / shuffle instructions
 // for four levels, where one butterfly over 32 lanes per level took 45 per level.
+// (Not inlined, scalar arguments: the code exists once per kernel instead of once per unrolled phase,
+// and the caller's column state stays in registers.)
+struct TmaRed {
+    unsigned wbuf;   // shared address of the warp's staging ring (lane 0's slot 0)
+    unsigned lvl, acc;
+    float psmin, psurf, wv, whalf;
+    int kdone, lane;
+};
 template <int NP>
-__device__ __forceinline__ void tma_reduce_batch(TmaCtx<NP>& c, int nlev) {
+__device__ __noinline__ void tma_reduce_batch(const TmaRed c, int nlev) {
     const unsigned full = 0xffffffffu;
     constexpr int NV = 2 * NP + 1;
     const int i = c.lane >> 3, sub = c.lane & 7;
     const int kk = c.kdone + i;
     const bool on = i < nlev;
-    const unsigned base = (c.buf - c.lane * 16) + (kk & (kStage - 1)) * (kThreads * 16) + sub * 16;
+    const unsigned base = c.wbuf + (kk & (kStage - 1)) * (kThreads * 16) + sub * 16;
     __syncwarp();  // the staged values were written by other lanes
     float4 v[4];
 #pragma unroll
@@ -307,7 +315,6 @@ __device__ __forceinline__ void tma_reduce_batch(TmaCtx<NP>& c, int nlev) {
         else if (NP == 2 ? ((sub & 1) == 0) : ((sub & 3) == 0)) sts32(dst + f * 4, lds32(dst + f * 4) + tot);
     }
     __syncwarp();  // the zeros are in place before any lane stages into these slots again
-    c.kdone += nlev;
 }
 
 // Reduces the staged levels every lane of the warp has passed, [c.kdone, min over lanes of k), four
@@ -322,39 +329,76 @@ __device__ __forceinline__ void tma_reduce(TmaCtx<NP>& c) {
         if (n <= 0) return;
         if ((int)__reduce_max_sync(full, (unsigned)c.k) - c.kdone < kStage - 1) return;
     }
+    TmaRed r;
+    r.wbuf = c.buf - c.lane * 16; r.lvl = c.lvl; r.acc = c.acc;
+    r.psmin = c.psmin; r.psurf = c.psurf; r.wv = c.wv; r.whalf = c.whalf; r.lane = c.lane;
     while (n > 0) {
-        tma_reduce_batch<NP>(c, n < 4 ? n : 4);
+        const int nl = n < 4 ? n : 4;
+        r.kdone = c.kdone;
+        tma_reduce_batch<NP>(r, nl);
+        c.kdone += nl;
         n -= 4;
     }
 }
 
-// output edges inside the current source layer (all remaining ones when it is the last layer):
-// each is evaluated once, its weighted values (mask and column weight folded into the scale) go
-// into the lane's staging ring -- NaNs are dealt with when the level is reduced
-template <int NP, bool LAST>
-__device__ __forceinline__ void tma_emit(TmaCtx<NP>& c) {
+// One pass of the edge loop: evaluates the next output edge of EVERY lane; the lanes that have none
+// in this layer (`can` false) run along predicated off, so the body is straight-line code.  The
+// weighted values (mask and column weight folded into the scale) go into the lane's staging ring --
+// NaNs are dealt with when the level is reduced.  CHECK: some lane may be more than kStage levels
+// ahead of the slowest lane of its warp (steep terrain inside the warp's patch; rare): those lanes
+// add their values straight into the accumulators.
+template <int NP, bool LAST, bool CHECK>
+__device__ __forceinline__ void tma_edge_pass(TmaCtx<NP>& c, bool can) {
     const unsigned full = 0xffffffffu;
-    while (true) {
-        // the level table ends with a +inf sentinel: lanes that are through never qualify
-        const bool can = LAST ? (c.k < c.km) : (c.pb <= c.m.pe_hi);
-        if (!__any_sync(full, can)) break;
-        const bool over = can && (c.k - c.kdone >= kStage);
-        const unsigned overmask = __ballot_sync(full, over);  // != 0: steep terrain inside the warp's patch, rare
+    unsigned overmask = 0;
+    if (CHECK) overmask = __ballot_sync(full, can && (c.k - c.kdone >= kStage));
+    f2 o[NP];
+    // 1/thickness, the column weight and the below-surface mask enter as one factor
+    // (MASK_NONE: thr = -inf; level 0: thr = +inf, see kernel)
+    const float scale = (c.thr < c.psurf) ? c.rdpc * c.wv : 0.f;
+    c.m.template edge<LAST>(c.pt, c.pb, scale, o, can, LAST ? c.m.Q[1] : nullptr);  // the last layer runs at phase 1
+    if (CHECK && overmask != 0) {
         if (can) {
-            f2 o[NP];
-            // 1/thickness, the column weight and the below-surface mask enter as one factor
-            // (MASK_NONE: thr = -inf; level 0: thr = +inf, see kernel)
-            const float scale = (c.thr < c.psurf) ? c.rdpc * c.wv : 0.f;
-            c.m.template edge<LAST>(c.pt, c.pb, scale, o);
-            if (over) tma_accumulate_slow<NP>(c.acc, c.k, c.lane, unpack4<NP>(o), overmask);
+            if ((overmask >> c.lane) & 1u) tma_accumulate_slow<NP>(c.acc, c.k, c.lane, unpack4<NP>(o), overmask);
             else sts128(c.buf + (c.k & (kStage - 1)) * (kThreads * 16), unpack4<NP>(o));
-            c.pt = c.pb;
-            c.k++;
-            const float4 lv = lds128(c.lvl + c.k * 16);
-            c.pb = lv.x; c.rdpc = lv.y; c.thr = lv.z;
+        }
+    } else {
+        if (can) sts128(c.buf + (c.k & (kStage - 1)) * (kThreads * 16), unpack4<NP>(o));
+    }
+    if (can) {
+        c.pt = c.pb;
+        c.k++;
+        const float4 lv = lds128(c.lvl + c.k * 16);
+        c.pb = lv.x; c.rdpc = lv.y; c.thr = lv.z;
+    }
+}
+
+// output edges inside the current source layer (all remaining ones when it is the last layer).
+// Common case (no lane within two levels of overflowing its staging ring, at most two edges per
+// lane in this layer): two unrolled passes without the overflow test.  general: the layer's edge
+// values may be NaN next to a finite mean (boundary layers, NaN level in the stencil): close_general.
+// QI = slot of the current layer's mean in the window (its phase).
+template <int NP, bool LAST, int QI>
+__device__ __forceinline__ void tma_emit(TmaCtx<NP>& c, bool general) {
+    const unsigned full = 0xffffffffu;
+    // the level table ends with a +inf sentinel: lanes that are through never qualify
+    bool can = LAST ? (c.k < c.km) : (c.pb <= c.m.pe_hi);
+    if (!LAST && !__any_sync(full, c.k - c.kdone >= kStage - 2)) {
+        tma_edge_pass<NP, LAST, false>(c, can);
+        can = c.pb <= c.m.pe_hi;
+        if (__any_sync(full, can)) {
+            tma_edge_pass<NP, LAST, false>(c, can);
+            can = c.pb <= c.m.pe_hi;
         }
     }
-    if (!LAST) c.m.close(c.pt);
+    while (__any_sync(full, can)) {
+        tma_edge_pass<NP, LAST, true>(c, can);
+        can = LAST ? (c.k < c.km) : (c.pb <= c.m.pe_hi);
+    }
+    if (!LAST) {
+        if (general) c.m.close_general(c.pt, c.m.Q[QI]);  // (warp-uniform)
+        else c.m.close(c.pt);
+    }
     tma_reduce<NP, LAST>(c);
 }
 
@@ -372,32 +416,36 @@ __device__ __forceinline__ void tma_read(unsigned src, f2 (&q)[NP], float& d) {
     for (int p = 0; p < NP; p++) q[p] = f2_make(v[2 * p], v[2 * p + 1]);
 }
 
-// enter interior source layer L (PH = L%4; 1 <= L <= km-3)
+// Interior source layer L (PH = L%4; 1 <= L <= km-3): step to it, emit its output edges.  Level
+// L+2 is already in the window (slot (PH+2)%4, loaded by the previous call); level L+3 is read
+// from the ring into the free slot (PH+3)%4 right after the step was issued, so that neither the
+// barrier wait nor the shared-memory latency sits in front of the arithmetic.
+// c.nanwin (warp-uniform) > 0: a NaN level is inside the stencil of some lane -> literal limiter tests.
 template <int NP, int NFL, int PH>
-__device__ __forceinline__ void tma_enter(TmaCtx<NP>& c, const TmaRing<NFL + 1>& rg, const TmaMaps& maps, unsigned src0, int L) {
-    f2 qn[NP];
-    if (L >= 2) {
-        // level L+2 lives in slot (PH+2)&3 of the current half; slot 0 starts the next half
-        constexpr int slot = (PH + 2) & 3;
+__device__ __forceinline__ void tma_layer(TmaCtx<NP>& c, const TmaRing<NFL + 1>& rg, const TmaMaps& maps, unsigned src0, int L) {
+    const unsigned full = 0xffffffffu;
+    const bool general = (L == 1) || (c.nanwin > 0);  // layer 1: its upper edge value comes from the top boundary formula
+    c.nanwin = c.nanwin > 0 ? c.nanwin - 1 : 0;
+    const float pn = c.pacc;  // pe[L+3]
+    if (L + 3 < c.km) {
+        // level L+3 lives in slot (PH+3)&3; slot 0 starts the next half
+        constexpr int slot = (PH + 3) & 3;
         if (slot == 0) {
             c.par ^= (c.hoff != 0);  // a new round of the ring begins when half 0 comes up again
             c.hoff = TmaSmem<NFL + 1>::half - c.hoff;
         }
         float d;
         mbar_wait(rg.full(c.hoff, slot), c.par);
-        tma_read<NP, NFL>(src0 + c.hoff + slot * (NFL + 1) * kTmaTile, qn, d);
-        rg.release(maps, c.hoff, slot, L + 2, c.km, c.lane);
+        tma_read<NP, NFL>(src0 + c.hoff + slot * (NFL + 1) * kTmaTile, c.m.Q[slot], d);
+        rg.release(maps, c.hoff, slot, L + 3, c.km, c.lane);
         c.pacc = c.pacc + nan_to_zero(d);
-        f2 s2 = qn[0];
-        if (NP == 2) s2 = f2_add(s2, qn[NP - 1]);
-        const float s = f2_lo(s2) + f2_hi(s2);
-        c.nanwin = (s != s) ? 5 : c.nanwin;  // NaN (or inf - inf) entering this column's stencil: rare
-    } else {  // L == 1: q[3] and pe[4] are left over from init()
-#pragma unroll
-        for (int p = 0; p < NP; p++) qn[p] = c.m.Q[3][p];
+        f2 s2 = c.m.Q[slot][0];
+        if (NP == 2) s2 = f2_add(s2, c.m.Q[slot][NP - 1]);
+        const float sv = f2_lo(s2) + f2_hi(s2);
+        if (__any_sync(full, sv != sv)) c.nanwin = 4;  // NaN (or inf - inf) entering the stencil: rare
     }
-    c.nanwin = c.nanwin > 0 ? c.nanwin - 1 : 0;
-    c.m.template step<PH>(c.pacc, qn, L == 1 || c.nanwin > 0);
+    c.m.template step_inplace<PH>(pn, general);
+    tma_emit<NP, false, PH>(c, general);
 }
 
 template <int NFL>
@@ -442,9 +490,11 @@ __device__ __forceinline__ void pc_gather_tail(const FieldPtrs<NFL>& fp, const f
     }
 }
 
-// CTAS: resident CTAs per SM the instance is compiled for (register cap: 3 -> 80, 2 -> 128)
-template <int NP, int NFL, int CTAS>
-__global__ void __launch_bounds__(kThreads, CTAS)
+// KR = (km - 3) % 4: the number of interior layers left over by the loop of four phases -- a template
+// parameter so that the unrolled loop has ONE exit (with exits between the phases ptxas brings the
+// rotating window back to canonical registers after every phase: 22 MOV per level)
+template <int NP, int NFL, int KR>
+__global__ void __launch_bounds__(kThreads, 2)
 pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL> fp,
                             const float* __restrict__ w, int64_t ws0, int64_t wsy,
                             float* __restrict__ delp_coarse, int km, int64_t ny, int64_t nx, float toa,
@@ -644,7 +694,7 @@ pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL>
                 dd[2 * i] = f2_lo(qD[i]); dd[2 * i + 1] = f2_hi(qD[i]);
                 s += (a[2 * i] + a[2 * i + 1]) + (b[2 * i] + b[2 * i + 1]) + (cc2[2 * i] + cc2[2 * i + 1]) + (dd[2 * i] + dd[2 * i + 1]);
             }
-            c.nanwin = (s != s) ? 5 : 0;
+            c.nanwin = __any_sync(0xffffffffu, s != s) ? 5 : 0;  // warp-uniform
             c.m.init(p, a, b, cc2, dd, iv);
             // output level 0 copies the top source layer (mappm.f90:62-64): its weighted sums go
             // straight into the accumulators; the edge that closes level 0 still runs (it opens
@@ -660,30 +710,28 @@ pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL>
             const bool fwriter = NP == 2 ? ((lane & 7) == 0) : ((lane & 15) == 0);
             if (fwriter) sts32(c.acc + (NP == 2 ? (lane >> 3) : (lane >> 4)) * 4, tot);  // accumulators start at zero
         }
-        tma_emit<NP, false>(c);  // layer 0 (km >= 4: never the last)
-        // interior layers: the windows rotate by renaming (four instances of the layer step,
-        // selected by a uniform branch); the edge / staging / reduction code exists once
+        tma_emit<NP, false, 0>(c, true);  // layer 0 (km >= 4: never the last)
+        // interior layers: the windows rotate by renaming -- the loop is unrolled by four phases,
+        // every phase with its own copy of the step AND of the edge code, so that no register is
+        // moved where the phases meet
+        const int Lend = km - 3;  // last interior layer; Lend % 4 == KR
+        int L = 1;
 #pragma unroll 1
-        for (int L = 1; L <= km - 3; L++) {
-            switch (L & 3) {
-                case 1: tma_enter<NP, NFL, 1>(c, rg, maps, src0, L); break;
-                case 2: tma_enter<NP, NFL, 2>(c, rg, maps, src0, L); break;
-                case 3: tma_enter<NP, NFL, 3>(c, rg, maps, src0, L); break;
-                default: tma_enter<NP, NFL, 0>(c, rg, maps, src0, L); break;
-            }
-            tma_emit<NP, false>(c);
+        for (; L + 3 <= Lend; L += 4) {
+            tma_layer<NP, NFL, 1>(c, rg, maps, src0, L);
+            tma_layer<NP, NFL, 2>(c, rg, maps, src0, L + 1);
+            tma_layer<NP, NFL, 3>(c, rg, maps, src0, L + 2);
+            tma_layer<NP, NFL, 0>(c, rg, maps, src0, L + 3);
         }
+        if (KR >= 1) tma_layer<NP, NFL, 1>(c, rg, maps, src0, L);
+        if (KR >= 2) tma_layer<NP, NFL, 2>(c, rg, maps, src0, L + 1);
+        if (KR >= 3) tma_layer<NP, NFL, 3>(c, rg, maps, src0, L + 2);
+        c.m.template rotate_to0<(KR + 1) & 3>();  // layer km-2 is entered at phase 0
         // the two bottom layers, once, at phase 0 / 1
-        switch ((km - 2) & 3) {
-            case 1: c.m.template rotate_to0<1>(); break;
-            case 2: c.m.template rotate_to0<2>(); break;
-            case 3: c.m.template rotate_to0<3>(); break;
-            default: break;
-        }
         c.m.template step_bottom<0>(iv);
-        tma_emit<NP, false>(c);
+        tma_emit<NP, false, 0>(c, true);
         c.m.template step_last<1>();
-        tma_emit<NP, true>(c);
+        tma_emit<NP, true, 1>(c, true);
     }
     __syncthreads();
 
@@ -743,9 +791,9 @@ inline bool tma_encode_field(CUtensorMap* m, const void* base, int64_t nb0, int 
 }
 
 // returns B200CS_OK, an error, or -1 when the arrays cannot be described to TMA (caller falls back)
-template <int NP, int NFL, int CTAS>
+template <int NP, int NFL, int KR>
 int launch_pc_tma(const PcArgs& a, int first) {
-    auto kern = pressure_coarsen_tma_kernel<NP, NFL, CTAS>;
+    auto kern = pressure_coarsen_tma_kernel<NP, NFL, KR>;
     const size_t smem = pressure_coarsen_tma_smem<NP, NFL>(a.km);
     if (smem > 227 * 1024) return -1;
     TmaMaps maps;
@@ -782,20 +830,28 @@ inline bool pc_tma_eligible(const PcArgs& a) {
 }
 
 // fields [first, ...) in groups of 4 / 3 / 2 / 1; -1: not describable to TMA (nothing was launched)
-template <int CTAS>
-int launch_pc_tma_fields(const PcArgs& a) {
+template <int KR>
+int launch_pc_tma_fields_kr(const PcArgs& a) {
     int first = 0;
     while (first < a.nfields) {
         const int left = a.nfields - first;
         int rc, n;
-        if (left >= 4) { rc = launch_pc_tma<2, 4, CTAS>(a, first); n = 4; }
-        else if (left == 3) { rc = launch_pc_tma<2, 3, CTAS>(a, first); n = 3; }
-        else if (left == 2) { rc = launch_pc_tma<1, 2, CTAS>(a, first); n = 2; }
-        else { rc = launch_pc_tma<1, 1, CTAS>(a, first); n = 1; }
+        if (left >= 4) { rc = launch_pc_tma<2, 4, KR>(a, first); n = 4; }
+        else if (left == 3) { rc = launch_pc_tma<2, 3, KR>(a, first); n = 3; }
+        else if (left == 2) { rc = launch_pc_tma<1, 2, KR>(a, first); n = 2; }
+        else { rc = launch_pc_tma<1, 1, KR>(a, first); n = 1; }
         if (rc != B200CS_OK) return rc;
         first += n;
     }
     return B200CS_OK;
+}
+inline int launch_pc_tma_fields(const PcArgs& a) {
+    switch ((a.km - 3) & 3) {
+        case 0: return launch_pc_tma_fields_kr<0>(a);
+        case 1: return launch_pc_tma_fields_kr<1>(a);
+        case 2: return launch_pc_tma_fields_kr<2>(a);
+        default: return launch_pc_tma_fields_kr<3>(a);
+    }
 }
 
 }  // namespace b200cs

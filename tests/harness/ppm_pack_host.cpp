@@ -12,7 +12,7 @@ struct Col {
     int km, kn, k; float pt; bool opened;
 
     template <int PH>
-    void emit(bool last) {
+    void emit(bool last, bool general) {
         if (!opened && (pe2[0] <= m.pe_hi || last)) { m.open_edge(pe2[0]); opened = true; }
         if (opened) {
             while (k < kn && (pe2[k + 1] <= m.pe_hi || last)) {
@@ -23,18 +23,21 @@ struct Col {
                     continue;
                 }
                 b200cs::f2 o2[NP];
-                m.edge(pt, pe2[k + 1], 1.0f / (pe2[k + 1] - pt), o2);
+                if (last) m.template edge<true>(pt, pe2[k + 1], 1.0f / (pe2[k + 1] - pt), o2, true, m.Q[PH]);
+                else m.template edge<false>(pt, pe2[k + 1], 1.0f / (pe2[k + 1] - pt), o2);
                 float o[NL];
                 for (int j = 0; j < NP; j++) { o[2 * j] = b200cs::f2_lo(o2[j]); o[2 * j + 1] = b200cs::f2_hi(o2[j]); }
                 for (int f = 0; f < NF; f++) out[f][k] = (pt <= pe1[0]) ? qp[f][0] : o[f];  // mappm.f90:62-64
                 pt = pe2[k + 1];
                 k++;
             }
-            m.close(pt);
+            if (general) m.close_general(pt, m.Q[PH]);
+            else m.close(pt);
         }
     }
     template <int PH>
     void layer(int L) {
+        bool general = true;  // boundary layers: literal limiter tests, NaN-safe close
         if (L >= 1 && L <= km - 3) {
             b200cs::f2 qn[NP];
             for (int j = 0; j < NP; j++) qn[j] = b200cs::f2_make(qp[2 * j][L + 2], qp[(2 * j + 1) % NF][L + 2]);
@@ -43,14 +46,15 @@ struct Col {
             bool nan_in = false;
             for (int f = 0; f < NF; f++) nan_in |= (qp[f][L + 2] != qp[f][L + 2]);
             if (nan_in) nanwin = 4;
-            m.template step<PH>(pe1[L + 3], qn, L == 1 || nanwin > 0);
+            general = L == 1 || nanwin > 0;
+            m.template step<PH>(pe1[L + 3], qn, general);
             if (nanwin > 0) nanwin--;
         } else if (L == km - 2) {
             m.template step_bottom<PH>(iv);
         } else if (L == km - 1) {
             m.template step_last<PH>();
         }
-        emit<PH>(L == km - 1);
+        emit<PH>(L == km - 1, general);
     }
     int iv, nanwin;
     void run() {

@@ -144,6 +144,31 @@ def test_fast_multifield_nans_and_known_answers(harness, oracle, golden):
         np.testing.assert_almost_equal(r, golden[f"mappm_kat|{case}|expected"], decimal=5)
 
 
+@pytest.mark.parametrize("kn", [79, 40, 25])
+def test_fast_nan_levels_whole_layers(harness, oracle, kn):
+    """NaN levels under output layers that swallow whole source layers: a source layer next to a NaN
+    level has NaN edge values but a finite mean, and enters an output layer that contains it entirely
+    through that mean (mappm.f90:99-104) -- per-column NaN patterns must match the oracle (in the
+    fused kernel a column that is wrongly NaN drops out of its coarse cell: 1/64 of the value)."""
+    rng = np.random.default_rng(77 + kn)
+    ncol, km = 400, 79
+    pe1, pe2 = hybrid_columns(rng, ncol, km)
+    if kn != km:
+        b = np.linspace(0, 1, kn + 1) ** 1.6
+        pe2 = pe2[:, :1] + (pe2[:, -1:] - pe2[:, :1]) * b[None]
+    pe1, pe2 = pe1.astype(np.float32), pe2.astype(np.float32)
+    qs = [(rng.normal(size=(ncol, km)) * s + o).astype(np.float32) for s, o in ((1.0, 0.0), (30.0, 250.0))]
+    qs[0][rng.uniform(size=qs[0].shape) < 0.02] = np.nan
+    qs[1][rng.uniform(size=qs[1].shape) < 0.004] = np.nan
+    qs[1][::9, -1] = np.nan
+    qs[0][::7, 0] = np.nan
+    qs[1][3::9, -3] = np.nan   # NaN just above the surface, finite bottom layer: output layers below the
+    qs[0][5::11, -2] = np.nan  # surface copy q[km-1] (mappm.f90:52-54) whatever lies above
+    got = run_fast(harness, pe1, qs, pe2, 1)
+    for g, q in zip(got, qs):
+        check(g, oracle.mappm(pe1, q, pe2), local_scale(pe1, q, pe2), 3e-6)
+
+
 def test_fast_terminates_on_non_monotone_pressures(harness):
     """Reference UB; the fast machine only promises to terminate without touching memory out of range."""
     pe1 = np.array([[1.0, 2.0, 3.0, 2.5, 2.6, 2.7]])
