@@ -38,6 +38,7 @@ constexpr int kTmaSlots = 8;          // level ring depth: two halves of 4 slots
 constexpr int kTmaTile = 1024;        // bytes of one array-level tile (8 rows x 128 B)
 constexpr int kTmaKA = 8;             // Phase A: levels per delp tile
 constexpr int kTmaMaxArrays = 5;      // 4 fields + delp
+constexpr int kTmaMaxChunks = 16;     // Phase A: delp tiles in flight (km <= 128)
 
 struct TmaMaps {
     CUtensorMap lvl[kTmaMaxArrays];   // [NFL] fields, then delp: box (32, 8, 1, 1)
@@ -67,20 +68,25 @@ __device__ __forceinline__ void tma_load4(unsigned dst, const CUtensorMap* map, 
         ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(z), "r"(b), "r"(bar) : "memory");
 }
 
-// shared memory carve-up (bytes from the 1 KB-aligned base); fixed-size parts first.  The level ring
-// is two HALVES of 4 slots; a half holds its tiles, its four "full" barriers and its four release
-// counters at the same offsets, so that ONE register (0 or kHalf) selects the half for all three.
+// shared memory carve-up (bytes from the 1 KB-aligned base).  Small fixed parts first, then the level
+// ring (two HALVES of 4 slots of NA tiles; ONE register, 0 or `half`, selects the half: tiles at
+// ring + hoff, the half's four "full" barriers at bars + (hoff >> 8), its four release counters at
+// cnts + (hoff >> 9)), the staging ring, the accumulators, the level tables.  Phase A borrows
+// ring + stage + accumulators (contiguous) for its delp tiles: 84 KB at NA = 5, km = 79 -- the whole
+// column of the tile in flight at once.
 template <int NA>
 struct TmaSmem {
-    static constexpr int half = 4 * NA * kTmaTile + 1024;               // tiles of 4 slots, then barriers / counters
-    static constexpr int hbar = 4 * NA * kTmaTile;                      // u64 full[4] of the half
-    static constexpr int hcnt = hbar + 32;                              // unsigned released[4] of the half
-    static constexpr int ring = 0;
-    static constexpr int stage = ring + 2 * half;                       // float4 [kStage][256]; Phase A: 4 delp tiles of 8 KB
-    static constexpr int w = stage + kStage * kThreads * 16;            // float [8][32] weights (NaN -> 0)
+    static constexpr int w = 0;                                         // float [8][32] weights (NaN -> 0)
     static constexpr int den = w + kTileY * kTileX * 4;                 // float [4] cell weight sums
-    static constexpr int bar_a = den + 16;                              // u64 fullA[4] (Phase A tiles)
-    static constexpr int lvl = bar_a + 32;                              // float4 [4][LS] level tables; then float acc[8][km][NV]
+    static constexpr int bars = den + 16;                               // u64 full[2][4] of the ring, 32 B per half at stride half >> 8
+    static constexpr int cnts = bars + 256;                             // unsigned released[2][4], 16 B per half at stride half >> 9
+    static constexpr int bar_a = cnts + 128;                            // u64 fullA[kTmaMaxChunks] (Phase A tiles)
+    static constexpr int ring = 2048;
+    static constexpr int half = 4 * NA * kTmaTile;                      // tiles of 4 slots
+    static constexpr int stage = ring + 2 * half;                       // float4 [kStage][256]
+    static constexpr int acc = stage + kStage * kThreads * 16;          // float [8][km][NV]; then float4 [4][LS] level tables
+    static_assert((half >> 8) >= 32 && 2 * (half >> 8) <= 256 && (half >> 9) >= 16 && 2 * (half >> 9) <= 128, "ring bookkeeping strides");
+    static_assert(bar_a + 8 * 16 <= ring, "fixed part overflows");
 };
 
 // keeps a cheap-to-recompute value in its register (ptxas rematerialises address arithmetic inside the hot loop)
@@ -114,13 +120,13 @@ struct TmaRing {
     unsigned sb;          // shared address of the carve-up's base
     unsigned nact;        // warps that consume the ring
     // hoff = 0 or TmaSmem<NA>::half
-    __device__ __forceinline__ unsigned full(unsigned hoff, int slot) const { return sb + hoff + TmaSmem<NA>::hbar + slot * 8; }
+    __device__ __forceinline__ unsigned full(unsigned hoff, int slot) const { return sb + TmaSmem<NA>::bars + (hoff >> 8) + slot * 8; }
     __device__ __forceinline__ void issue(const TmaMaps& maps, unsigned hoff, int slot, int level) const {
         const unsigned bar = full(hoff, slot);
         mbar_expect_tx(bar, NA * kTmaTile);
 #pragma unroll
         for (int i = 0; i < NA; i++)
-            tma_load4(sb + hoff + (slot * NA + i) * kTmaTile, &maps.lvl[i], (int)(blockIdx.x * kTileX), (int)(blockIdx.y * kTileY),
+            tma_load4(sb + TmaSmem<NA>::ring + hoff + (slot * NA + i) * kTmaTile, &maps.lvl[i], (int)(blockIdx.x * kTileX), (int)(blockIdx.y * kTileY),
                       level, (int)blockIdx.z, bar);
     }
     // every lane of the warp has read its values of `level` from (hoff, slot): the last warp to say
@@ -129,7 +135,7 @@ struct TmaRing {
     __device__ __forceinline__ void release(const TmaMaps& maps, unsigned hoff, int slot, int level, int km, int lane) const {
         if (lane == 0) {
             unsigned old;
-            asm volatile("atom.shared.inc.u32 %0, [%1], %2;" : "=r"(old) : "r"(sb + hoff + TmaSmem<NA>::hcnt + slot * 4), "r"(nact - 1) : "memory");
+            asm volatile("atom.shared.inc.u32 %0, [%1], %2;" : "=r"(old) : "r"(sb + TmaSmem<NA>::cnts + (hoff >> 9) + slot * 4), "r"(nact - 1) : "memory");
             if (old == nact - 1) {
                 if (level + kTmaSlots < km) issue(maps, hoff, slot, level + kTmaSlots);
             }
@@ -518,11 +524,12 @@ pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL>
     // (volatile: ptxas otherwise re-derives the window address -- S2R SR_CgaCtaId + LEA -- at every use)
     const unsigned sbase = opaque((unsigned)__cvta_generic_to_shared(smem_raw));
     const int LS = sweep_lvl_stride(km);
-    float4* s_lvl = reinterpret_cast<float4*>(smem_raw + SM::lvl);            // [CW][LS], last = sentinel
-    float* s_acc = reinterpret_cast<float*>(s_lvl + (size_t)CW * LS);         // [8 warps][km][NV]
+    float* s_acc = reinterpret_cast<float*>(smem_raw + SM::acc);              // [8 warps][km][NV]
+    float4* s_lvl = reinterpret_cast<float4*>(s_acc + (size_t)8 * km * NV);   // [CW][LS], last = sentinel (16-byte aligned: km * NV * 32 bytes)
     float* s_w = reinterpret_cast<float*>(smem_raw + SM::w);                  // [8][32]
     float* s_den = reinterpret_cast<float*>(smem_raw + SM::den);              // [CW]
     const unsigned bar_a = sbase + SM::bar_a;
+    const unsigned lvl_sh = sbase + SM::acc + 8 * km * NV * 4;
 
     TmaRing<NA> rg;
     rg.sb = sbase;
@@ -530,32 +537,30 @@ pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL>
         const int64_t left = nx - (int64_t)blockIdx.x * kTileX;
         rg.nact = left >= kTileX ? 8u : (unsigned)(left / 8) * 2u;
     }
+    // Phase A streams the tile's delp in chunks of kTmaKA levels (8 KB); ring + staging ring +
+    // accumulators hold nbuf of them at once (all ten at NA = 5, km = 79)
     const int nchunk = (km + kTmaKA - 1) / kTmaKA;
+    int nbuf = (2 * SM::half + kStage * kThreads * 16 + 8 * km * NV * 4) / (kTmaKA * kTmaTile);
+    nbuf = nbuf < nchunk ? nbuf : nchunk;
+    nbuf = nbuf < kTmaMaxChunks ? nbuf : kTmaMaxChunks;
+    const unsigned tiles_a = sbase + SM::ring;
     if (tid == 0) {
 #pragma unroll
         for (int i = 0; i < 4; i++) {
             mbar_init(rg.full(0, i), 1);
             mbar_init(rg.full(SM::half, i), 1);
-            mbar_init(bar_a + i * 8, 1);
-            sts32(sbase + SM::hcnt + i * 4, 0.f);
-            sts32(sbase + SM::half + SM::hcnt + i * 4, 0.f);
+            sts32(sbase + SM::cnts + i * 4, 0.f);
+            sts32(sbase + SM::cnts + (SM::half >> 9) + i * 4, 0.f);
         }
+        for (int i = 0; i < nbuf; i++) mbar_init(bar_a + i * 8, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        // Phase A's first four delp tiles, then levels 0..7 of the ring
-#pragma unroll
-        for (int cch = 0; cch < 4; cch++) {
-            if (cch < nchunk) {
-                mbar_expect_tx(bar_a + cch * 8, kTmaKA * kTmaTile);
-                tma_load4(sbase + SM::stage + cch * kTmaKA * kTmaTile, &maps.dchunk, (int)(blockIdx.x * kTileX),
-                          (int)(blockIdx.y * kTileY), cch * kTmaKA, (int)b0, bar_a + cch * 8);
-            }
+        for (int cch = 0; cch < nbuf; cch++) {
+            mbar_expect_tx(bar_a + cch * 8, kTmaKA * kTmaTile);
+            tma_load4(tiles_a + cch * kTmaKA * kTmaTile, &maps.dchunk, (int)(blockIdx.x * kTileX),
+                      (int)(blockIdx.y * kTileY), cch * kTmaKA, (int)b0, bar_a + cch * 8);
         }
-#pragma unroll
-        for (int j = 0; j < kTmaSlots; j++)
-            if (j < km) rg.issue(maps, j < 4 ? 0u : (unsigned)SM::half, j & 3, j);
     }
-    for (int t = tid; t < 8 * km * NV; t += kThreads) s_acc[t] = 0.f;
 
     // ---------------- Phase A: coarse pressure levels of the tile's cells -------------------
     const float wv = active ? __ldg(w + b0 * ws0 + yg * wsy + xg) : 0.f;
@@ -574,20 +579,16 @@ pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL>
     __syncthreads();
     float pacc = toa;
 #pragma unroll 1
-    for (int ch = 0; ch < nchunk; ch++) {
-        const int bufi = ch & 3;
-        const unsigned tile = sbase + SM::stage + bufi * kTmaKA * kTmaTile;
-        mbar_wait(bar_a + bufi * 8, ((unsigned)ch >> 2) & 1u);
-        {   // fine surface pressure: sequential fp32 cumsum of the column (xarray cumsum == nancumsum)
-            float d[kTmaKA];
-#pragma unroll
-            for (int kk = 0; kk < kTmaKA; kk++) d[kk] = lds32(tile + kk * kTmaTile + my_off);
-#pragma unroll
-            for (int kk = 0; kk < kTmaKA; kk++) pacc = pacc + nan_to_zero(d[kk]);  // levels beyond km read as 0
-        }
-        if (wid == (ch & 7)) {
-            // one lane per (level, cell): 64 products delp*w in numpy's order (rows pairwise, then
-            // row after row), straight from the swizzled tile; bit-identical to the EXACT kernel
+    for (int c0 = 0; c0 < nchunk; c0 += nbuf) {  // rounds of nbuf chunks (one round when everything fits)
+        const unsigned rpar = (unsigned)(c0 / nbuf) & 1u;
+        const int cend = c0 + nbuf < nchunk ? c0 + nbuf : nchunk;
+        // coarse delp: warp (ch % 8) takes chunk ch as soon as it has landed, one lane per
+        // (level, cell): 64 products delp*w in numpy's order (rows pairwise, then row after row),
+        // straight from the swizzled tile; bit-identical to the EXACT kernel
+#pragma unroll 1
+        for (int ch = c0 + wid; ch < cend; ch += 8) {
+            const unsigned tile = tiles_a + (ch - c0) * kTmaKA * kTmaTile;
+            mbar_wait(bar_a + (ch - c0) * 8, rpar);
             const int kk = lane >> 2, cc = lane & 3, k = ch * kTmaKA + kk;
             const unsigned lt = tile + kk * kTmaTile;
             float num = 0.f;
@@ -614,12 +615,37 @@ pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL>
                 if (delp_coarse && cxg < cxN) delp_coarse[((b0 * km + k) * cyN + cyg) * cxN + cxg] = dc;
             }
         }
-        __syncthreads();  // everybody is through with this tile
-        if (tid == 0 && ch + 4 < nchunk) {
-            mbar_expect_tx(bar_a + bufi * 8, kTmaKA * kTmaTile);
-            tma_load4(tile, &maps.dchunk, (int)(blockIdx.x * kTileX), (int)(blockIdx.y * kTileY), (ch + 4) * kTmaKA, (int)b0, bar_a + bufi * 8);
+        // fine surface pressure: sequential fp32 cumsum of the column (xarray cumsum == nancumsum),
+        // every thread through all chunks in level order
+#pragma unroll 1
+        for (int ch = c0; ch < cend; ch++) {
+            const unsigned tile = tiles_a + (ch - c0) * kTmaKA * kTmaTile;
+            mbar_wait(bar_a + (ch - c0) * 8, rpar);
+            float d[kTmaKA];
+#pragma unroll
+            for (int kk = 0; kk < kTmaKA; kk++) d[kk] = lds32(tile + kk * kTmaTile + my_off);
+#pragma unroll
+            for (int kk = 0; kk < kTmaKA; kk++) pacc = pacc + nan_to_zero(d[kk]);  // levels beyond km read as 0
+        }
+        __syncthreads();  // everybody is through with these tiles
+        if (tid == 0 && cend < nchunk) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            for (int ch = cend; ch < cend + nbuf && ch < nchunk; ch++) {
+                mbar_expect_tx(bar_a + (ch - cend) * 8, kTmaKA * kTmaTile);
+                tma_load4(tiles_a + (ch - cend) * kTmaKA * kTmaTile, &maps.dchunk, (int)(blockIdx.x * kTileX), (int)(blockIdx.y * kTileY),
+                          ch * kTmaKA, (int)b0, bar_a + (ch - cend) * 8);
+            }
         }
     }
+    // the delp tiles are done with: levels 0..7 of all arrays into the ring (delp from L2 now), while
+    // the level tables are finished below
+    if (tid == 0) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#pragma unroll
+        for (int jj = 0; jj < kTmaSlots; jj++)
+            if (jj < km) rg.issue(maps, jj < 4 ? 0u : (unsigned)SM::half, jj & 3, jj);
+    }
+    for (int t = tid; t < 8 * km * NV; t += kThreads) s_acc[t] = 0.f;
     // coarse interfaces: the cumsum is sequential (exact)
     if (tid < CW) {
         float pc = toa;
@@ -663,8 +689,8 @@ pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL>
         TmaCtx<NP> c;
         c.km = km; c.lane = lane;
         c.wv = wv; c.whalf = whalf; c.psurf = pacc;
-        c.lvl = sbase + SM::lvl + (wid >> 1) * LS * 16;
-        c.acc = sbase + SM::lvl + CW * LS * 16 + wid * km * NV * 4;
+        c.lvl = lvl_sh + (wid >> 1) * LS * 16;
+        c.acc = sbase + SM::acc + wid * km * NV * 4;
         c.buf = sbase + SM::stage + tid * 16;
         c.par = 0;
         c.hoff = 0;  // levels 0..3 (init) come from half 0; level 4 flips to half 1
@@ -756,7 +782,7 @@ pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL>
 template <int NP, int NFL>
 size_t pressure_coarsen_tma_smem(int km) {
     constexpr int NV = 2 * NP + 1, CW = kTileX / 8;
-    return (size_t)TmaSmem<NFL + 1>::lvl + (size_t)CW * sweep_lvl_stride(km) * sizeof(float4) +
+    return (size_t)TmaSmem<NFL + 1>::acc + (size_t)CW * sweep_lvl_stride(km) * sizeof(float4) +
            sizeof(float) * (size_t)8 * km * NV + 1024;  // + alignment slack
 }
 
