@@ -50,7 +50,8 @@ def _compile(unit):
     deps = [os.path.join(HERE, src), os.path.abspath(__file__)] + [os.path.join(HERE, h) for h in HEADERS]
     if not _stale(obj, deps):
         return name, "", False
-    cmd = [NVCC] + ARCH + COMMON + flags + ["-c", os.path.join(HERE, src), "-o", obj]
+    extra = os.environ.get("B200CS_DEV_NVCC_FLAGS", "").split()  # developer experiments only (e.g. -DB200CS_TMA_HALVES=1)
+    cmd = [NVCC] + ARCH + COMMON + flags + extra + ["-c", os.path.join(HERE, src), "-o", obj]
     p = subprocess.run(cmd, capture_output=True, text=True)
     if p.returncode != 0:
         raise RuntimeError(f"nvcc failed for {name}:\n{' '.join(cmd)}\n{p.stdout}\n{p.stderr}")

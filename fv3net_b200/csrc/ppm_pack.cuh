@@ -132,8 +132,9 @@ struct PpmPack {
         const float ml1 = min3abs(f2_hi(dl), f2_hi(tr2), f2_hi(X));
         const float mr0 = min3abs(f2_lo(dr), f2_lo(tl2), f2_lo(X));
         const float mr1 = min3abs(f2_hi(dr), f2_hi(tl2), f2_hi(X));
-        DL[p] = f2_make(xor_nsign(ml0, f2_lo(dr)), xor_nsign(ml1, f2_hi(dr)));  // -s min(|dl|, 2|dr|)
-        DR[p] = f2_make(xor_sign(mr0, f2_lo(dr)), xor_sign(mr1, f2_hi(dr)));    //  s min(|dr|, 2|dl|)
+        // dl and dr have opposite signs (or the layer is flat): -s = sign(dl), one LOP3 each
+        DL[p] = f2_make(xor_sign(ml0, f2_lo(dl)), xor_sign(ml1, f2_hi(dl)));  // -s min(|dl|, 2|dr|)
+        DR[p] = f2_make(xor_sign(mr0, f2_lo(dr)), xor_sign(mr1, f2_hi(dr)));  //  s min(|dr|, 2|dl|)
         AL[p] = f2_add(a1, DL[p]);
         AR[p] = f2_add(a1, DR[p]);
     }

@@ -18,6 +18,8 @@ from fv3net_b200 import core, restarts  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--n", type=int, default=384)
 ap.add_argument("--reps", type=int, default=10)
+ap.add_argument("--modes", default="fast,exact")
+ap.add_argument("--warm", type=int, default=3)
 ap.add_argument("--rough", action="store_true",
                 help="surface pressure U(5e4, 1.04e5) independently per column instead of bench.py's smooth field + "
                      "1.5 kPa noise: neighbouring columns then cross very different numbers of coarse levels per "
@@ -62,7 +64,9 @@ def run(mode):
 
 res = {}
 for name, mode in (("fast", core.FAST), ("exact", core.EXACT)):
-    for _ in range(3):
+    if name not in args.modes.split(","):
+        continue
+    for _ in range(args.warm):
         run(mode)
     torch.cuda.synchronize()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.reps + 1)]
