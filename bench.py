@@ -588,8 +588,11 @@ def main():
     # N > 1: each rank's coarse outputs land in one contiguous buffer (no staging copy) and are
     # all-gathered asynchronously -- the gather of step i runs under the kernel of step i + 1
     # (double-buffered); the last one is waited for inside the timed region.
-    nbuf = 2
     use_peer = world > 1 and args.collective == "peer" and mode == core.FAST
+    # fused gather: THREE buffers, so that the kernel of step i waits for the barrier of step i-2 (a whole step old) and
+    # never for the one that follows the previous kernel (with two buffers every kernel start paid the barrier latency
+    # and the skew between ranks: 0.935 at N=2)
+    nbuf = 3 if use_peer else 2
     pending = [None] * nbuf
     counter = [0]
     if use_peer:
@@ -618,10 +621,11 @@ def main():
         i = counter[0] % nbuf
         counter[0] += 1
         if use_peer:
-            # Ordering, with two buffers and the barriers on a SIDE stream (off the kernels' critical path):
+            # Ordering, with three buffers and the barriers on a SIDE stream (off the kernels' critical path):
             #   readers of buffer i wait for the barrier after the kernel that wrote it (bar_done[i]);
-            #   the kernel that REUSES buffer i (two steps later) waits for the barrier of the step in
-            #   between, which every peer enters only after it has consumed buffer i (side-stream order).
+            #   the kernel that REUSES buffer i (three steps later) waits for the barrier of the step after the
+            #   one that wrote it -- bar_done[(i + 1) % 3], two steps old by then --, which every peer enters only
+            #   after it has consumed buffer i (side-stream order).
             comp = torch.cuda.current_stream()
             j = (i + 1) % nbuf
             if bar_done[j] is not None:
@@ -816,7 +820,7 @@ def main():
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "kernel": "one fused launch per step",
                    "arithmetic_mode": args.mode, "terrain": args.terrain, "l2": "inputs (1.42 GB) larger than L2, no flush needed",
-                   "per_rank": "one synthetic timestep per GPU (weak)", "collective": ("none" if world == 1 else "fused: the coarsening kernel stores its coarse outputs (21.8 MB/rank) into every rank's gather buffer over NVLink peer memory, one device-side barrier per step on a side stream (two buffers)" if use_peer else "NCCL all_gather of the coarse outputs (21.8 MB/rank), asynchronous: overlaps the next step")},
+                   "per_rank": "one synthetic timestep per GPU (weak)", "collective": ("none" if world == 1 else "fused: the coarsening kernel stores its coarse outputs (21.8 MB/rank) into every rank's gather buffer over NVLink peer memory, one device-side barrier per step on a side stream (three buffers)" if use_peer else "NCCL all_gather of the coarse outputs (21.8 MB/rank), asynchronous: overlaps the next step")},
         "clocks": clocks,
         "other_mode": {"arithmetic_mode": "exact" if args.mode == "fast" else "fast", "kernel_ms": other_ms},
         "parity_slab": None if slab_err is None else {

@@ -82,6 +82,58 @@ B200CS_HD float xor_nsign(float a, float s) {
 #endif
 }
 
+// ---- per-column geometry, shared by every field of the column (and, in the warp-specialised kernel,
+// computed by other threads than the field math: pressure_coarsen_ws.cuh) ---------------------------
+struct PpmStepGeo { float A, B, G1, G2, nG3; };
+// slope factors of layer L+1 and edge-value factors of interface L+1 from dp[L-1..L+2]
+// (mappm.f90:658-683); r01 = 1/(dp0+dp1) formed by the previous step, rn = 1/(dp1+dp2) for the next
+B200CS_HD PpmStepGeo ppm_step_geo(float dpm, float dp0, float dp1, float dp2, float r01, float& rn) {
+    const float Pm0 = dpm + dp0, P01 = dp0 + dp1, P12 = dp1 + dp2;
+    rn = fast_rcp(P12);
+    const float t = dp1 * fast_rcp(P01 + dp2);
+    PpmStepGeo o;
+    o.A = t * (dp0 + 0.5f * dp1) * rn;
+    o.B = t * (dp2 + 0.5f * dp1) * r01;
+    const float a1 = Pm0 * fast_rcp(P01 + dp0);
+    const float a2 = P12 * fast_rcp(P01 + dp1);
+    const float g = 2.f * fast_rcp(Pm0 + P12);
+    const float gd0 = g * dp1;
+    o.G1 = (dp0 * r01) * (1.f + gd0 * (a1 - a2));
+    o.G2 = gd0 * a2;
+    o.nG3 = -(g * dp0 * a1);
+    return o;
+}
+// an output edge pb inside (or, last layer, below) the source layer [pe_lo, pe_hi]: what the
+// anchored integrals of the fields need (header): h, c1 = s(1+t), c2 = s t; last layer: the
+// stretch below the surface and the two whole-layer cases
+struct PpmEdgeGeo { float h, c1, c2, ext; bool whole, below; };
+template <bool LAST>
+B200CS_HD PpmEdgeGeo ppm_edge_geo(float pt, float pb, float pe_lo, float pe_hi, float rdp0) {
+    PpmEdgeGeo o;
+    o.h = (LAST ? fminf(pb, pe_hi) : pb) - pe_lo;
+    const float g = LAST ? fmaxf(pe_hi - pb, 0.f) : pe_hi - pb;
+    const float s = o.h * rdp0, t = g * rdp0;
+    o.c2 = s * t;
+    o.c1 = s + o.c2;
+    // below the surface the last layer's mean carries on (:118-123); a last layer that lies
+    // entirely inside the output layer enters through its mean (:99-104), whatever its edge values
+    o.ext = LAST ? fmaxf(pb - fmaxf(pt, pe_hi), 0.f) : 0.f;
+    o.whole = LAST && !(pt > pe_lo) && pb > pe_hi;
+    o.below = LAST && !(pt < pe_hi);  // output layer entirely below the surface: q[km-1] whatever lies above (:52-54)
+    return o;
+}
+// leaving the layer: what lies below its last output edge pt
+struct PpmCloseGeo { float g, e1, e2; bool whole; };
+B200CS_HD PpmCloseGeo ppm_close_geo(float pt, float pe_lo, float pe_hi, float rdp0) {
+    PpmCloseGeo o;
+    o.g = pe_hi - fmaxf(pt, pe_lo);
+    const float t = o.g * rdp0, sv = 1.f - t;
+    o.e2 = sv * t;
+    o.e1 = t + o.e2;
+    o.whole = !(pt > pe_lo);  // an edge AT pe_lo belongs to the layer above (edges are emitted while pb <= pe_hi)
+    return o;
+}
+
 template <int NP>
 struct PpmPack {
     static constexpr int NF = 2 * NP;
@@ -143,6 +195,16 @@ struct PpmPack {
     B200CS_HD void init(const float (&p)[5], const float (&qA)[NF], const float (&qB)[NF],
                         const float (&qC)[NF], const float (&qD)[NF], int iv) {
         const float d1 = p[1] - p[0], d2 = p[2] - p[1], d3 = p[3] - p[2], d4 = p[4] - p[3];
+        init_fields(d1, d2, d3, d4, qA, qB, qC, qD, iv);
+        PE[0] = p[0]; PE[1] = p[1]; PE[2] = p[2]; PE[3] = p[3];
+        DP[0] = d1; DP[1] = d2; DP[2] = d3; DP[3] = d4;
+        r12 = fast_rcp(d2 + d3);
+        rdp0 = fast_rcp(d1);
+        pe_lo = p[0]; pe_hi = p[1];
+    }
+    // ... the field part alone (d1..d4 = dp[0..3])
+    B200CS_HD void init_fields(float d1, float d2, float d3, float d4, const float (&qA)[NF], const float (&qB)[NF],
+                               const float (&qC)[NF], const float (&qD)[NF], int iv) {
         float s2[NF], s3[NF], e3[NF];
         PpmStream<NF>::slope(qA, qB, qC, d1, d2, d3, s2);          // dc[1]
         PpmStream<NF>::slope(qB, qC, qD, d2, d3, d4, s3);          // dc[2]
@@ -187,11 +249,6 @@ struct PpmPack {
             R[j] = f2_bc(0.f);
             parabola_general(j, f2_make(x1v[a], x1v[b]), E[1][j], Q[0][j], f2_make(dc0v[a], dc0v[b]));
         }
-        PE[0] = p[0]; PE[1] = p[1]; PE[2] = p[2]; PE[3] = p[3];
-        DP[0] = d1; DP[1] = d2; DP[2] = d3; DP[3] = d4;
-        r12 = fast_rcp(d2 + d3);
-        rdp0 = fast_rcp(d1);
-        pe_lo = p[0]; pe_hi = p[1];
     }
 
     // Enter interior layer L (1 <= L <= km-3), PH = L%4.  pn = pe[L+3], qn = q[L+2].
@@ -217,19 +274,15 @@ struct PpmPack {
         pe_lo = PE[i0]; pe_hi = PE[i1];
         const float r01 = r12;
         rdp0 = fast_rcp(dp0);
-        const float Pm0 = dpm + dp0, P01 = dp0 + dp1, P12 = dp1 + dp2;
-        const float rn = fast_rcp(P12);
-        r12 = rn;
-        const float t = dp1 * fast_rcp(P01 + dp2);
-        const float A = t * (dp0 + 0.5f * dp1) * rn;
-        const float B = t * (dp2 + 0.5f * dp1) * r01;
-        const float a1 = Pm0 * fast_rcp(P01 + dp0);
-        const float a2 = P12 * fast_rcp(P01 + dp1);
-        const float g = 2.f * fast_rcp(Pm0 + P12);
-        const float gd0 = g * dp1;
-        const float G1 = (dp0 * r01) * (1.f + gd0 * (a1 - a2));
-        const float G2 = gd0 * a2;
-        const float nG3 = -(g * dp0 * a1);
+        const PpmStepGeo geo = ppm_step_geo(dpm, dp0, dp1, dp2, r01, r12);
+        step_fields<PH>(geo, general);
+    }
+    // ... the field part alone
+    template <int PH>
+    B200CS_HD void step_fields(const PpmStepGeo& geo, bool general) {
+        constexpr int i0 = PH, i1 = (PH + 1) & 3, i2 = (PH + 2) & 3;
+        constexpr int e0 = PH & 1, e1 = (PH + 1) & 1;
+        const float A = geo.A, B = geo.B, G1 = geo.G1, G2 = geo.G2, nG3 = geo.nG3;
 #pragma unroll
         for (int p = 0; p < NP; p++) {
             const f2 q0 = Q[i0][p], q1 = Q[i1][p];
@@ -289,10 +342,16 @@ struct PpmPack {
     template <int PH>
     B200CS_HD void step_bottom(int iv) {
         constexpr int i0 = PH, i1 = (PH + 1) & 3;
-        constexpr int e0 = PH & 1, e1 = (PH + 1) & 1;
         const float d2 = DP[i0], d1 = DP[i1];  // dp[km-2], dp[km-1]
         pe_lo = PE[i0]; pe_hi = PE[i1];
         rdp0 = fast_rcp(d2);
+        step_bottom_fields<PH>(d2, d1, iv);
+    }
+    // ... the field part alone (d2 = dp[km-2], d1 = dp[km-1])
+    template <int PH>
+    B200CS_HD void step_bottom_fields(float d2, float d1, int iv) {
+        constexpr int i0 = PH, i1 = (PH + 1) & 3;
+        constexpr int e0 = PH & 1, e1 = (PH + 1) & 1;
         const float s = d1 + d2;
         const float den = d2 * (2.f * d2 * d2 + d1 * (d2 + 3.f * d1));
         const float t5 = d2 * (5.f * d1 + d2) - 3.f * d1 * d1;
@@ -335,9 +394,14 @@ struct PpmPack {
     template <int PH>
     B200CS_HD void step_last() {
         constexpr int i0 = PH, i1 = (PH + 1) & 3;
-        constexpr int e0 = PH & 1, e1 = (PH + 1) & 1;
         pe_lo = PE[i0]; pe_hi = PE[i1];
         rdp0 = fast_rcp(DP[i0]);
+        step_last_fields<PH>();
+    }
+    template <int PH>
+    B200CS_HD void step_last_fields() {
+        constexpr int i0 = PH;
+        constexpr int e0 = PH & 1, e1 = (PH + 1) & 1;
 #pragma unroll
         for (int p = 0; p < NP; p++) parabola_general(p, E[e0][p], E[e1][p], Q[i0][p], DC[e0][p]);
     }
@@ -349,53 +413,43 @@ struct PpmPack {
     // lanes of a warp that have no edge in this layer run along).
     template <bool LAST = true>
     B200CS_HD void edge(float pt, float pb, float scale, f2 (&out)[NP], bool on = true, const f2* qm = nullptr) {
-        const float h = (LAST ? fminf(pb, pe_hi) : pb) - pe_lo;
-        const float g = LAST ? fmaxf(pe_hi - pb, 0.f) : pe_hi - pb;
-        const float s = h * rdp0, t = g * rdp0;
-        const float c2 = s * t, c1 = s + c2;
-        // below the surface the last layer's mean carries on (:118-123); a last layer that lies
-        // entirely inside the output layer enters through its mean (:99-104), whatever its edge values
-        const float ext = LAST ? fmaxf(pb - fmaxf(pt, pe_hi), 0.f) : 0.f;
-        const bool whole = LAST && !(pt > pe_lo) && pb > pe_hi;
-        const bool below = LAST && !(pt < pe_hi);  // output layer entirely below the surface: q[km-1] whatever lies above (:52-54)
+        edge_fields<LAST>(ppm_edge_geo<LAST>(pt, pb, pe_lo, pe_hi, rdp0), scale, out, on, qm);
+    }
+    // ... the field part alone
+    template <bool LAST = true>
+    B200CS_HD void edge_fields(const PpmEdgeGeo& eg, float scale, f2 (&out)[NP], bool on, const f2* qm) {
 #pragma unroll
         for (int p = 0; p < NP; p++) {
-            f2 P = f2_fma(f2_bc(-c2), DR[p], f2_fma(f2_bc(-c1), DL[p], AL[p]));
-            if (LAST) P = whole ? qm[p] : P;
-            f2 m = f2_fma(f2_bc(h), P, R[p]);
-            if (LAST) m = below ? f2_mul(f2_bc(ext), qm[p]) : f2_fma(f2_bc(ext), qm[p], m);
+            f2 P = f2_fma(f2_bc(-eg.c2), DR[p], f2_fma(f2_bc(-eg.c1), DL[p], AL[p]));
+            if (LAST) P = eg.whole ? qm[p] : P;
+            f2 m = f2_fma(f2_bc(eg.h), P, R[p]);
+            if (LAST) m = eg.below ? f2_mul(f2_bc(eg.ext), qm[p]) : f2_fma(f2_bc(eg.ext), qm[p], m);
             out[p] = f2_mul(m, f2_bc(scale));
-            const f2 nI = f2_mul(f2_bc(-h), P);
+            const f2 nI = f2_mul(f2_bc(-eg.h), P);
             if (on) R[p] = nI;
         }
     }
 
     // Leaving the current layer: what lies below its last output edge pt (the whole layer when pt
-    // is not inside it, :99-104) opens the mass of the output layer being filled.  An edge AT
-    // pe_lo belongs to the layer above (edges are emitted while pb <= pe_hi).
-    B200CS_HD void close(float pt) {
-        const float g = pe_hi - fmaxf(pt, pe_lo);
-        const float t = g * rdp0, sv = 1.f - t;
-        const float e2 = sv * t, e1 = t + e2;
-        const float keep = (pt > pe_lo) ? 0.f : 1.f;
+    // is not inside it, :99-104) opens the mass of the output layer being filled.
+    B200CS_HD void close(float pt) { close_fields(ppm_close_geo(pt, pe_lo, pe_hi, rdp0)); }
+    B200CS_HD void close_fields(const PpmCloseGeo& cg) {
+        const float keep = cg.whole ? 1.f : 0.f;
 #pragma unroll
         for (int p = 0; p < NP; p++) {
-            const f2 P = f2_fma(f2_bc(-e2), DL[p], f2_fma(f2_bc(-e1), DR[p], AR[p]));
-            R[p] = f2_fma(f2_bc(g), P, f2_mul(f2_bc(keep), R[p]));
+            const f2 P = f2_fma(f2_bc(-cg.e2), DL[p], f2_fma(f2_bc(-cg.e1), DR[p], AR[p]));
+            R[p] = f2_fma(f2_bc(cg.g), P, f2_mul(f2_bc(keep), R[p]));
         }
     }
     // ... for layers whose edge values may be NaN (a NaN level inside the stencil): a layer without
     // an output edge enters through its mean q, as in the reference, and after an edge the mass
     // above it is dropped, not multiplied by zero
-    B200CS_HD void close_general(float pt, const f2 (&q)[NP]) {
-        const float g = pe_hi - fmaxf(pt, pe_lo);
-        const float t = g * rdp0, sv = 1.f - t;
-        const float e2 = sv * t, e1 = t + e2;
-        const bool whole = !(pt > pe_lo);
+    B200CS_HD void close_general(float pt, const f2 (&q)[NP]) { close_general_fields(ppm_close_geo(pt, pe_lo, pe_hi, rdp0), q); }
+    B200CS_HD void close_general_fields(const PpmCloseGeo& cg, const f2 (&q)[NP]) {
 #pragma unroll
         for (int p = 0; p < NP; p++) {
-            const f2 P = f2_fma(f2_bc(-e2), DL[p], f2_fma(f2_bc(-e1), DR[p], AR[p]));
-            R[p] = whole ? f2_fma(f2_bc(g), q[p], R[p]) : f2_mul(f2_bc(g), P);
+            const f2 P = f2_fma(f2_bc(-cg.e2), DL[p], f2_fma(f2_bc(-cg.e1), DR[p], AR[p]));
+            R[p] = cg.whole ? f2_fma(f2_bc(cg.g), q[p], R[p]) : f2_mul(f2_bc(cg.g), P);
         }
     }
 

@@ -3,12 +3,24 @@
 #include "pressure_coarsen_fast.cuh"
 #include "pressure_coarsen_sweep.cuh"
 #include "pressure_coarsen_tma.cuh"
+#ifdef B200CS_WITH_WS  // experimental warp-specialised kernel: developer builds only
+#include <stdlib.h>
+
+#include "pressure_coarsen_ws.cuh"
+#endif
 
 namespace b200cs {
 bool pc_fast_covers(const PcArgs& a, int field_dtype, int p_dtype, int w_dtype) {
     return pc_fast_eligible(a, field_dtype, p_dtype, w_dtype);
 }
 int pc_fast_entry(const PcArgs& a) {
+#ifdef B200CS_WITH_WS
+    static const int ws = [] { const char* e = getenv("B200CS_DEV_WS"); return e ? atoi(e) : 0; }();
+    if (ws && pc_tma_eligible(a)) {
+        const int rc = launch_pc_ws_fields(a);
+        if (rc != -1) return rc;
+    }
+#endif
     if (pc_tma_eligible(a)) {
         // TMA-fed kernel; -1: the arrays cannot be described to TMA (alignment, strides) -> sweep kernel
         const int rc = launch_pc_tma_fields(a);

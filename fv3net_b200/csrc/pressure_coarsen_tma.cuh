@@ -62,6 +62,22 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
         "DONE:\n"
         "}" ::"r"(bar), "r"(parity) : "memory");
 }
+// ... for the role that runs AHEAD of the other one (warp-specialised kernel: the geometry warps): it
+// sleeps between polls instead of taking issue slots from the warps it is waiting for.  (A
+// suspend-time hint on try_wait changed nothing: 91 polls per level and warp either way.)
+__device__ __forceinline__ void mbar_wait_sleep(unsigned bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE;\n"
+        "LAB_WAIT:\n"
+        "nanosleep.u32 200;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@!P1 bra LAB_WAIT;\n"
+        "DONE:\n"
+        "}" ::"r"(bar), "r"(parity) : "memory");
+}
 __device__ __forceinline__ void tma_load4(unsigned dst, const CUtensorMap* map, int x, int y, int z, int b, unsigned bar) {
     asm volatile(
         "cp.async.bulk.tensor.4d.shared::cta.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
