@@ -476,16 +476,19 @@ __device__ __forceinline__ void pc_gather_tail(const FieldPtrs<NFL>& fp, const f
     // The CTAs of one row of tiles (same blockIdx.y, b0) produce one complete coarse row.  The
     // last of them to finish copies that row -- contiguous cxN-float segments, read back through
     // L2 -- into this rank's slot on every peer with 16-byte stores over NVLink.
+    // One release-acquire atomic by thread 0 after the CTA barrier (cumulative over the Phase C stores
+    // of all warps) decides; r01 had every thread fence first (+65 us per launch at C384, 5 % --
+    // tools/gather_diag.py).  (Leaving the copy to warp 0 alone so that the other warps need not wait
+    // for the atomic was far worse: 1.50 ms per step at N = 2.)
     __shared__ int s_last;
-    __threadfence();
     __syncthreads();
     if (tid == 0) {
-        const int prev = atomicAdd(&peers.counters[b0 * gridDim.y + blockIdx.y], 1);
+        int prev;
+        asm volatile("atom.add.acq_rel.gpu.global.s32 %0, [%1], 1;" : "=r"(prev) : "l"(peers.counters + (b0 * gridDim.y + blockIdx.y)) : "memory");
         s_last = (prev == (int)gridDim.x - 1);
     }
     __syncthreads();
     if (!s_last) return;
-    __threadfence();
     const int64_t cy0 = blockIdx.y;  // kTileY / 8 = 1 coarse row per row of tiles
     const bool vec = (cxN % 4 == 0);
     const int64_t per_row = vec ? cxN / 4 : cxN;
@@ -778,6 +781,44 @@ pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL>
     __syncthreads();
 
     // ---------------- Phase C: the two halves of a cell, divide, store -----------------------
+    // Fused all-gather (b200cs_pressure_coarsen_gather), common case: the tile's four coarse values of
+    // one (level, field) are 16 contiguous bytes of the output row -- each goes to the local output
+    // and straight into this rank's slot of every peer's gather buffer with one 16-byte store over
+    // NVLink.  No counters, no fences, nobody waits: the stores of a CTA ride under the arithmetic of
+    // the CTAs that follow (the r01 scheme -- last CTA of a tile row copies the finished row -- made every
+    // CTA wait for a device-scope atomic and moved the data in bursts at the ends of the waves:
+    // +65 us per launch at C384, 5 %; tools/gather_diag.py).
+    bool vecg = peers.n > 0 && (cxN % 4 == 0) && ((int64_t)blockIdx.x * CW + CW <= cxN) && (peers.field_elems % 4 == 0);
+    if (vecg) {
+#pragma unroll
+        for (int i = 0; i < NFL; i++) vecg = vecg && (((uintptr_t)fp.out[i] & 15) == 0);
+        for (int p = 0; p < peers.n; p++) vecg = vecg && (((uintptr_t)peers.base[p] & 15) == 0);
+    }
+    if (vecg) {
+        const bool with_delp = (first == 0 && delp_coarse != nullptr);
+        const int nslot = NFL + (with_delp ? 1 : 0);
+        for (int t = tid; t < km * nslot; t += kThreads) {
+            const int k = t / nslot, i = t % nslot;
+            float v[4];
+#pragma unroll
+            for (int cc = 0; cc < CW; cc++) {
+                if (i < NFL) {
+                    const float* a = s_acc + ((size_t)(2 * cc) * km + k) * NV;
+                    const float* b = s_acc + ((size_t)(2 * cc + 1) * km + k) * NV;
+                    const float den = a[2 * NP] + b[2 * NP];
+                    v[cc] = (a[i] + b[i]) / den;
+                } else {
+                    v[cc] = s_lvl[cc * LS + k].w;
+                }
+            }
+            const float4 v4 = make_float4(v[0], v[1], v[2], v[3]);
+            const int64_t o = ((b0 * km + k) * cyN + (int64_t)blockIdx.y) * cxN + (int64_t)blockIdx.x * CW;
+            if (i < NFL) *reinterpret_cast<float4*>((float*)fp.out[i] + o) = v4;
+            const int64_t slot = i < NFL ? (first + i) : peers.nfields;
+            for (int p = 0; p < peers.n; p++) *reinterpret_cast<float4*>(peers.base[p] + slot * peers.field_elems + o) = v4;
+        }
+        return;
+    }
     for (int t = tid; t < km * CW; t += kThreads) {
         const int cc = t % CW, k = t / CW;
         const int64_t cyg = blockIdx.y, cxg = (int64_t)blockIdx.x * CW + cc;
@@ -791,7 +832,7 @@ pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL>
         }
     }
 
-    // ---------------- fused all-gather (b200cs_pressure_coarsen_gather) ----------------------
+    // ---------------- fused all-gather, general case: the last CTA of a tile row copies the row ----
     if (peers.n > 0) pc_gather_tail<NFL>(fp, delp_coarse, peers, first, b0, km, cyN, cxN, tid);
 }
 
