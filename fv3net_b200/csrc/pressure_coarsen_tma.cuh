@@ -137,6 +137,8 @@ struct TmaRing {
     unsigned nact;        // warps that consume the ring
     // hoff = 0 or TmaSmem<NA>::half
     __device__ __forceinline__ unsigned full(unsigned hoff, int slot) const { return sb + TmaSmem<NA>::bars + (hoff >> 8) + slot * 8; }
+    // (inline on purpose: out of line -- one lane in 256 runs it per level -- the call's register
+    // constraints cost 8 %, 1.15 -> 1.24 ms)
     __device__ __forceinline__ void issue(const TmaMaps& maps, unsigned hoff, int slot, int level) const {
         const unsigned bar = full(hoff, slot);
         mbar_expect_tx(bar, NA * kTmaTile);
@@ -788,7 +790,9 @@ pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL>
     // the CTAs that follow (the r01 scheme -- last CTA of a tile row copies the finished row -- made every
     // CTA wait for a device-scope atomic and moved the data in bursts at the ends of the waves:
     // +65 us per launch at C384, 5 %; tools/gather_diag.py).
-    bool vecg = peers.n > 0 && (cxN % 4 == 0) && ((int64_t)blockIdx.x * CW + CW <= cxN) && (peers.field_elems % 4 == 0);
+    // (Two ranks only: with seven peers the 16-byte NVLink packets of all CTAs cost 295 us per launch, 0.80 weak-scaling
+    // efficiency at N = 8; there the finished rows are copied in 192-byte segments by the last CTA of a tile row, below.)
+    bool vecg = peers.n > 0 && peers.n <= 2 && (cxN % 4 == 0) && ((int64_t)blockIdx.x * CW + CW <= cxN) && (peers.field_elems % 4 == 0);
     if (vecg) {
 #pragma unroll
         for (int i = 0; i < NFL; i++) vecg = vecg && (((uintptr_t)fp.out[i] & 15) == 0);
