@@ -555,6 +555,9 @@ def main():
                     help="c384 (default): BASELINE.json's metric, one C384 timestep per GPU (weak scaling); "
                          "c3072: BASELINE configs[4], ONE C3072 -> C48 timestep (factor 64, delp + 4 fields, 89.7 GB) "
                          "sharded by (tile, coarse row) over the GPUs (strong scaling)")
+    ap.add_argument("--gather", default="auto", choices=["auto", "fused", "ce"],
+                    help="--collective peer: 'fused' = stores from the coarsening kernel itself, 'ce' = peer-to-peer DMA after "
+                         "the kernel, under the next one (auto: fused for two ranks, ce beyond)")
     ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
                     help="N>1: 'peer' = the coarsening kernel stores its coarse outputs into every rank's gather "
                          "buffer over NVLink peer memory (fused all-gather); 'nccl' = asynchronous NCCL all_gather")
@@ -615,6 +618,13 @@ def main():
         gathered = [torch.empty((world,) + tuple(mine[0].shape), dtype=torch.float32, device=dev) for _ in range(nbuf)] if world > 1 else None
 
     side = torch.cuda.Stream(device=dev) if use_peer else None
+    # --gather: 'fused' = the coarsening kernel itself stores into the peers (16-byte stores from its epilogue for two
+    # ranks, finished rows copied by the last CTA of a tile row beyond); 'ce' = plain kernel, then one peer-to-peer DMA per
+    # destination on copy streams (no SM involved), overlapped with the next step's kernel
+    use_ce = use_peer and (args.gather == "ce" or (args.gather == "auto" and world > 2))
+    if use_ce:
+        ce_streams = [torch.cuda.Stream(device=dev) for _ in range(min(world, 8))]
+        locals_ = [local, torch.empty_like(local), torch.empty_like(local)]
     bar_done = [None] * nbuf  # event: the barrier that follows the kernel which wrote buffer i has completed
 
     def step():
@@ -630,10 +640,22 @@ def main():
             j = (i + 1) % nbuf
             if bar_done[j] is not None:
                 comp.wait_event(bar_done[j])
-            outs, dco = core.pressure_coarsen(fields, delp, area, FACTOR, TOA, mask_mode="phalf", mode=mode, out=local,
-                                              peer_ptrs=gath[i].peer_ptrs)
+            if use_ce:
+                # local buffer i was last read by the DMAs of step i-3, which finished before the barrier awaited above
+                outs, dco = core.pressure_coarsen(fields, delp, area, FACTOR, TOA, mask_mode="phalf", mode=mode, out=locals_[i])
+            else:
+                outs, dco = core.pressure_coarsen(fields, delp, area, FACTOR, TOA, mask_mode="phalf", mode=mode, out=local,
+                                                  peer_ptrs=gath[i].peer_ptrs)
             wrote = torch.cuda.Event()
             wrote.record(comp)
+            if use_ce:
+                for st in ce_streams:
+                    st.wait_event(wrote)
+                    if bar_done[j] is not None:
+                        st.wait_event(bar_done[j])  # every peer has consumed what these DMAs overwrite
+                gath[i].push(locals_[i], ce_streams)
+                for st in ce_streams:
+                    side.wait_stream(st)
             side.wait_event(wrote)
             with torch.cuda.stream(side):
                 gath[i].barrier()  # all writers of buffer i are done: gath[i].buffer holds every rank's outputs
@@ -669,7 +691,7 @@ def main():
         del so, sd
     if use_peer:  # once, untimed: the peer-written buffer equals an NCCL all_gather of the same outputs
         ref = torch.empty((world,) + tuple(local.shape), dtype=torch.float32, device=dev)
-        dist.all_gather_into_tensor(ref, local)
+        dist.all_gather_into_tensor(ref, locals_[(counter[0] - 1) % nbuf] if use_ce else local)
         got = gath[(counter[0] - 1) % nbuf].buffer
         assert torch.equal(torch.nan_to_num(ref), torch.nan_to_num(got)), "fused gather differs from NCCL all_gather"
         del ref
@@ -820,7 +842,7 @@ def main():
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "kernel": "one fused launch per step",
                    "arithmetic_mode": args.mode, "terrain": args.terrain, "l2": "inputs (1.42 GB) larger than L2, no flush needed",
-                   "per_rank": "one synthetic timestep per GPU (weak)", "collective": ("none" if world == 1 else "fused: the coarsening kernel stores its coarse outputs (21.8 MB/rank) into every rank's gather buffer over NVLink peer memory, one device-side barrier per step on a side stream (three buffers)" if use_peer else "NCCL all_gather of the coarse outputs (21.8 MB/rank), asynchronous: overlaps the next step")},
+                   "per_rank": "one synthetic timestep per GPU (weak)", "collective": ("none" if world == 1 else ("peer-to-peer DMA (copy engines over NVLink, no SM) of the coarse outputs (21.8 MB/rank) into every rank's gather buffer after the kernel, under the next step's kernel; one device-side barrier per step on a side stream (three buffers)" if use_ce else "fused: the coarsening kernel stores its coarse outputs (21.8 MB/rank) into every rank's gather buffer over NVLink peer memory, one device-side barrier per step on a side stream (three buffers)") if use_peer else "NCCL all_gather of the coarse outputs (21.8 MB/rank), asynchronous: overlaps the next step")},
         "clocks": clocks,
         "other_mode": {"arithmetic_mode": "exact" if args.mode == "fast" else "fast", "kernel_ms": other_ms},
         "parity_slab": None if slab_err is None else {

@@ -27,6 +27,7 @@ class CoarseGather:
         slot_bytes = self.buffer[0].numel() * 4
         # this rank's slot inside every peer's buffer (its own included: that one is a local pointer)
         self.peer_ptrs = [int(p) + self.rank * slot_bytes for p in self.handle.buffer_ptrs]
+        self._peer_slots = None
 
     @property
     def mine(self):
@@ -35,3 +36,15 @@ class CoarseGather:
 
     def barrier(self, channel=0):
         self.handle.barrier(channel=channel)
+
+    def push(self, local, streams):
+        """Copy-engine variant: ``local`` ([nfields + 1, B, km, cy, cx], this rank's finished outputs) goes into slot
+        ``rank`` of every rank's buffer with one peer-to-peer cudaMemcpyAsync per destination, round-robin over
+        ``streams`` -- DMA engines over NVLink, no SM is involved, so the copies of step i run entirely under the
+        coarsening kernel of step i+1."""
+        if self._peer_slots is None:
+            shape = tuple(self.buffer.shape)
+            self._peer_slots = [self.handle.get_buffer(p, shape, torch.float32)[self.rank] for p in range(self.world)]
+        for p, dst in enumerate(self._peer_slots):
+            with torch.cuda.stream(streams[p % len(streams)]):
+                dst.copy_(local, non_blocking=True)
