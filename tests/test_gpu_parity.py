@@ -1004,21 +1004,24 @@ def test_budget_inputs_vs_oracle(core, oracle):
     assert eq(one, exp["T"]) and eq(dco, exp["delp"])
 
 
-def test_fused_gather_slots_single_gpu(core):
-    """b200cs_pressure_coarsen_gather with two 'peers' that are plain local buffers: every slot
-    receives exactly the kernel's outputs (fields in order, coarse delp last)."""
-    rng = np.random.default_rng(61)
-    nb, km, n, f = 2, 12, 32, 8
+@pytest.mark.parametrize("npeers,n", [(2, 32), (1, 64), (3, 32), (8, 64), (2, 40), (3, 40)])
+def test_fused_gather_slots_single_gpu(core, npeers, n):
+    """b200cs_pressure_coarsen_gather with 'peers' that are plain local buffers: every slot receives
+    exactly the kernel's outputs (fields in order, coarse delp last).  <= 2 peers take the 16-byte
+    direct stores of Phase C, more the last-CTA row copy; n = 40 has partial tiles and rows that are
+    not a multiple of four cells (scalar stores)."""
+    rng = np.random.default_rng(61 + npeers)
+    nb, km, f = 2, 12, 8
     delp = torch.as_tensor(_synthetic_columns(rng, nb, km, n, np.float32)).cuda()
     area = torch.as_tensor(rng.uniform(0.5, 1, size=(nb, n, n)).astype(np.float32)).cuda()
     fields = [torch.as_tensor(rng.normal(size=(nb, km, n, n)).astype(np.float32)).cuda() for _ in range(5)]  # 4 + 1 launches
     ref, dref = core.pressure_coarsen(fields, delp, area, f, mode=core.FAST)
-    slots = torch.zeros((2, len(fields) + 1, nb, km, n // f, n // f), dtype=torch.float32, device="cuda")
+    slots = torch.zeros((npeers, len(fields) + 1, nb, km, n // f, n // f), dtype=torch.float32, device="cuda")
     outs, dco = core.pressure_coarsen(fields, delp, area, f, mode=core.FAST,
-                                      peer_ptrs=[slots[0].data_ptr(), slots[1].data_ptr()])
+                                      peer_ptrs=[slots[s].data_ptr() for s in range(npeers)])
     torch.cuda.synchronize()
     exp = torch.stack(list(ref) + [dref])
-    for s in range(2):
+    for s in range(npeers):
         assert torch.equal(torch.nan_to_num(slots[s]), torch.nan_to_num(exp))
     assert all(torch.equal(torch.nan_to_num(a), torch.nan_to_num(b)) for a, b in zip(outs, ref))
     from fv3net_b200._lib import B200csError
