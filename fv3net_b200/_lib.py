@@ -27,7 +27,7 @@ EXPORTS = [
     "b200cs_dominant_mask", "b200cs_pressure_at_midpoint_log", "b200cs_exposed_area_weights",
     "b200cs_pressure_coarsen_gather", "b200cs_pressure_coarsen_gather_workspace_bytes",
     "b200cs_pressure_coarsen_wide", "b200cs_pressure_coarsen_wide_workspace_bytes", "b200cs_mappm_fast",
-    "b200cs_host_copy",
+    "b200cs_host_copy", "b200cs_mappm_static",
 ]
 
 _lib = None
@@ -65,6 +65,7 @@ def load():
     lib.b200cs_mappm_workspace_bytes.restype = i64
     lib.b200cs_mappm.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, i64, i32, i32, i32, i32,
                                  vp, i64, vp]
+    lib.b200cs_mappm_static.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, i64, i32, i32, i32, i32, vp]
     lib.b200cs_mappm_fast.argtypes = [vp, p64, vp, p64, vp, p64, vp, p64, i64, i64, i32, i32, i32, i32, vp]
     lib.b200cs_pressure_coarsen.argtypes = [i32, pvp, i32, p64, vp, i32, p64, vp, i32, p64, pvp, vp, i64, i32,
                                             i64, i64, i32, i32, dbl, i32, i32, i32, i32, vp]

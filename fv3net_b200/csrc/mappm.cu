@@ -12,6 +12,8 @@
 //     per-thread slot of a caller-provided global workspace laid out [level][slot]
 //     (coalesced across the threads of a warp), then remapped.
 // fp32 throughout like the Fortran build; compiled with -fmad=false.
+#include <mutex>
+
 #include "common.cuh"
 #include "ppm_stream.cuh"
 
@@ -423,4 +425,60 @@ extern "C" int b200cs_mappm(const float* pe1, int64_t pe1_cs, int64_t pe1_ls, co
         pe1, pe1_cs, pe1_ls, q1, q1_cs, q1_ls, pe2, pe2_cs, pe2_ls, q2, q2_cs, q2_ls, ncol, km, kn, iv, kord,
         (float*)workspace, nslot);
     return check_launch("mappm(generic)");
+}
+
+// ---------------------------------------------------------------------------------------------
+// b200cs_mappm_static: b200cs_mappm for callers that may not allocate (CUDA graph capture, serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The [level][slot] workspace of the kord > 6 machine lives in a file-scope
+// device array of B200CS_MAPPM_STATIC_MAX_BYTES that every GPU loading the library holds until
+// exit.  The kernel writes every workspace element before reading it (DP, then the profile planes,
+// per column), so nothing has to be cleared between calls; all calls on a device share the array,
+// so calls that overlap on the GPU (different streams) race.
+// ---------------------------------------------------------------------------------------------
+namespace b200cs {
+static __device__ __align__(256) float g_mappm_static_ws[B200CS_MAPPM_STATIC_MAX_BYTES / sizeof(float)];
+
+constexpr int kMaxStaticDevices = 64;
+static float* g_static_ws_ptr[kMaxStaticDevices] = {};
+static std::mutex g_static_ws_mutex;
+
+// device address of the array on the CURRENT device (the name above is a host-side stand-in in host
+// code, not an address a kernel can use); resolved once per device
+static int mappm_static_ws(float** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return set_err(B200CS_ECUDA, "mappm_static: cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= kMaxStaticDevices) return set_err(B200CS_EINVAL, "mappm_static: device %d out of range", dev);
+    std::lock_guard<std::mutex> lock(g_static_ws_mutex);
+    if (!g_static_ws_ptr[dev]) {
+        float* ptr = nullptr;
+        e = cudaGetSymbolAddress((void**)&ptr, g_mappm_static_ws);
+        if (e != cudaSuccess || !ptr)
+            return set_err(B200CS_ECUDA, "mappm_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        g_static_ws_ptr[dev] = ptr;
+    }
+    *out = g_static_ws_ptr[dev];
+    return B200CS_OK;
+}
+}  // namespace b200cs
+
+extern "C" int b200cs_mappm_static(const float* pe1, int64_t pe1_cs, int64_t pe1_ls, const float* q1, int64_t q1_cs,
+                                   int64_t q1_ls, const float* pe2, int64_t pe2_cs, int64_t pe2_ls, float* q2,
+                                   int64_t q2_cs, int64_t q2_ls, int64_t ncol, int km, int kn, int iv, int kord,
+                                   void* stream) {
+    float* ws = nullptr;
+    int64_t need = 0;
+    if (kord > 6 && ncol > 0 && km > 0) {
+        need = b200cs_mappm_workspace_bytes(ncol, km);
+        if (need > (int64_t)B200CS_MAPPM_STATIC_MAX_BYTES)
+            return set_err(B200CS_EWORKSPACE,
+                           "mappm_static: ncol=%lld, km=%d needs %lld workspace bytes, the static array holds %lld "
+                           "(use b200cs_mappm with a caller-provided workspace)",
+                           (long long)ncol, km, (long long)need, (long long)B200CS_MAPPM_STATIC_MAX_BYTES);
+        const int rc = mappm_static_ws(&ws);
+        if (rc != B200CS_OK) return rc;
+    }
+    return b200cs_mappm(pe1, pe1_cs, pe1_ls, q1, q1_cs, q1_ls, pe2, pe2_cs, pe2_ls, q2, q2_cs, q2_ls, ncol, km, kn, iv,
+                        kord, ws, need, stream);
 }

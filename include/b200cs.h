@@ -174,6 +174,25 @@ int b200cs_mappm(const float* pe1, int64_t pe1_cs, int64_t pe1_ls, const float* 
                  void* workspace, int64_t workspace_bytes, void* stream);
 
 /*
+ * b200cs_mappm without a caller-provided workspace and WITHOUT ANY ALLOCATION.  No counterpart in
+ * the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * arguments, kernels and results as b200cs_mappm; the workspace of the kord > 6 machine is a
+ * file-scope device array of B200CS_MAPPM_STATIC_MAX_BYTES that every GPU that loads the library
+ * holds until exit.  Limit: b200cs_mappm_workspace_bytes(ncol, km) <= B200CS_MAPPM_STATIC_MAX_BYTES
+ * (6553 columns of km = 79 per call), else B200CS_EWORKSPACE -- split the columns over calls or
+ * use b200cs_mappm.  kord <= 6 needs no workspace and has no limit.  All calls on one device
+ * share the array: calls that overlap on the GPU (different streams) race -- serialise them.
+ * The array keeps the previous call's contents; the kernel writes every element before it reads
+ * it, so nothing needs clearing.
+ */
+#define B200CS_MAPPM_STATIC_MAX_BYTES (16 * 1024 * 1024)
+int b200cs_mappm_static(const float* pe1, int64_t pe1_cs, int64_t pe1_ls, const float* q1, int64_t q1_cs,
+                        int64_t q1_ls, const float* pe2, int64_t pe2_cs, int64_t pe2_ls, float* q2,
+                        int64_t q2_cs, int64_t q2_ls, int64_t ncol, int km, int kn, int iv, int kord,
+                        void* stream);
+
+/*
  * mappm in B200CS_FAST arithmetic: the level search and the parabolas of MAPPM/mappm.f90:10-126,
  * 614-931 with the pressure geometry hoisted, rcp.approx for its reciprocals and FMA contraction
  * -- within 1e-6 relative of b200cs_mappm.  Only the lmt=0 profiles (kord <= 3; every reference
