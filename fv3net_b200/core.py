@@ -19,6 +19,7 @@ from . import _lib
 from ._lib import EXACT, FAST, MASK_NONE, MASK_PFULL, MASK_PHALF  # noqa: F401
 
 _DT = {torch.float32: _lib.F32, torch.float64: _lib.F64}
+_NP_OF = {torch.float32: np.float32, torch.float64: np.float64}
 _MASK = {None: MASK_NONE, "none": MASK_NONE, "phalf": MASK_PHALF, "pfull": MASK_PFULL}
 _OPS = {"sum": _lib.OP_SUM, "mean": _lib.OP_MEAN, "min": _lib.OP_MIN, "max": _lib.OP_MAX,
         "median": _lib.OP_MEDIAN, "mode": _lib.OP_MODE}
@@ -573,6 +574,7 @@ class _PinnedRing:
 
     def __init__(self, dev):
         self.dev, self.bytes, self.slots, self.free = dev, 0, [], []
+        self.out = None
         self.next = 0
         self.nthreads = max(1, min(32, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)))
 
@@ -585,6 +587,13 @@ class _PinnedRing:
         self.bytes = int(nbytes)
         self.slots = [torch.empty(self.bytes, dtype=torch.uint8).pin_memory() for _ in range(self.NSLOT)]
         self.free = [None] * self.NSLOT
+
+    def out_slab(self, nbytes):
+        """pinned slab for results on their way to the caller's numpy arrays; its contents are consumed
+        before the call that asked for it returns"""
+        if self.out is None or self.out.numel() < nbytes:
+            self.out = torch.empty(int(nbytes), dtype=torch.uint8).pin_memory()
+        return self.out
 
     def upload(self, src, dst, stream):
         """src: C-contiguous host tensor (pageable or pinned); dst: device tensor of the same dtype
@@ -655,8 +664,33 @@ def _pressure_coarsen_from_host(fields, delp, weights, f, toa_pressure, mask_mod
     outs = [torch.cat([o[i] for o in outs_t]) for i in range(len(hf))]
     dco = torch.cat(dco_t) if return_delp_coarse else None
     if was_np:
-        return [o.cpu().numpy() for o in outs], (dco.cpu().numpy() if dco is not None else None)
+        return _download_numpy(outs + ([dco] if dco is not None else []), ring, copy, comp, len(hf), dco is not None)
     return outs, dco
+
+
+def _download_numpy(tensors, ring, copy, comp, nf, with_dco):
+    """Device results -> fresh numpy arrays: ONE asynchronous DMA of all of them into a reused pinned
+    slab, one synchronisation, then an all-core copy into the arrays handed to the caller
+    (``Tensor.cpu()`` on each result is a synchronous staged copy through pageable memory: 2.3 ms per
+    4.4 MB array at C384 against 0.4 ms for all five this way)."""
+    sizes = [t.numel() * t.element_size() for t in tensors]
+    offs = [0]
+    for n in sizes:
+        offs.append(offs[-1] + ((n + 255) & ~255))
+    slab = ring.out_slab(offs[-1])
+    copy.wait_stream(comp)
+    with torch.cuda.stream(copy):
+        for t, o, n in zip(tensors, offs, sizes):
+            slab[o:o + n].view(t.dtype).view(t.shape).copy_(t, non_blocking=True)
+            t.record_stream(copy)
+    copy.synchronize()
+    res = []
+    lib = _lib.load()
+    for t, o, n in zip(tensors, offs, sizes):
+        a = np.empty(tuple(t.shape), dtype=_NP_OF[t.dtype])
+        _lib.check(lib.b200cs_host_copy(a.ctypes.data, slab.data_ptr() + o, n, ring.nthreads), "host_copy")
+        res.append(a)
+    return res[:nf], (res[nf] if with_dco else None)
 
 
 def gather_columns(a, step):
