@@ -557,7 +557,7 @@ def main():
                          "sharded by (tile, coarse row) over the GPUs (strong scaling)")
     ap.add_argument("--gather", default="auto", choices=["auto", "fused", "ce"],
                     help="--collective peer: 'fused' = stores from the coarsening kernel itself, 'ce' = peer-to-peer DMA after "
-                         "the kernel, under the next one (auto: fused for two ranks, ce beyond)")
+                         "the kernel, under the next one (auto = ce: measured faster at every N, 0.988 vs 0.979 at N=2, 0.961 vs 0.940 at N=8)")
     ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
                     help="N>1: 'peer' = the coarsening kernel stores its coarse outputs into every rank's gather "
                          "buffer over NVLink peer memory (fused all-gather); 'nccl' = asynchronous NCCL all_gather")
@@ -621,7 +621,7 @@ def main():
     # --gather: 'fused' = the coarsening kernel itself stores into the peers (16-byte stores from its epilogue for two
     # ranks, finished rows copied by the last CTA of a tile row beyond); 'ce' = plain kernel, then one peer-to-peer DMA per
     # destination on copy streams (no SM involved), overlapped with the next step's kernel
-    use_ce = use_peer and (args.gather == "ce" or (args.gather == "auto" and world > 2))
+    use_ce = use_peer and (args.gather == "ce" or (args.gather == "auto" and world > 1))
     if use_ce:
         ce_streams = [torch.cuda.Stream(device=dev) for _ in range(min(world, 8))]
         locals_ = [local, torch.empty_like(local), torch.empty_like(local)]
