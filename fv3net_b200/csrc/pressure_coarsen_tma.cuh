@@ -520,8 +520,14 @@ __device__ __forceinline__ void pc_gather_tail(const FieldPtrs<NFL>& fp, const f
 // KR = (km - 3) % 4: the number of interior layers left over by the loop of four phases -- a template
 // parameter so that the unrolled loop has ONE exit (with exits between the phases ptxas brings the
 // rotating window back to canonical registers after every phase: 22 MOV per level)
+// One- and two-field launches (NP = 1; the 13th field of a whole timestep) run three CTAs per SM at 80
+// registers (32-108 B of spills): 0.876 -> 0.768 ms for one field, 0.909 -> 0.806 ms for two at C384
+// (tools/nfield_time.py).  The four-field kernel spills 480 B at 80 registers and stays at two.
+#ifndef B200CS_NP1_CTAS
+#define B200CS_NP1_CTAS 3
+#endif
 template <int NP, int NFL, int KR>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, NP == 1 ? B200CS_NP1_CTAS : 2)
 pressure_coarsen_tma_kernel(const __grid_constant__ TmaMaps maps, FieldPtrs<NFL> fp,
                             const float* __restrict__ w, int64_t ws0, int64_t wsy,
                             float* __restrict__ delp_coarse, int km, int64_t ny, int64_t nx, float toa,
