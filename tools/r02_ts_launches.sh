@@ -7,7 +7,8 @@ python - <<'PY'
 import csv, collections
 rows = [r for r in csv.reader(open("gpurun_out/ts_launches.csv")) if len(r) > 5]
 hdr = rows[0]; ik = hdr.index("Kernel Name"); iv = hdr.index("Metric Value"); iu = hdr.index("Metric Unit")
-ks = [(r[ik], float(r[iv].replace(",", "")) * (1e-3 if r[iu] in ("us", "usecond") else (1e-6 if r[iu] in ("ns", "nsecond") else 1.0))) for r in rows[1:]]
+ks = [(r[ik], float(r[iv].replace(",", "")) * (1e-3 if r[iu] in ("us", "usecond") else (1e-6 if r[iu] in ("ns", "nsecond") else 1.0))) for r in rows[1:]
+      if "b200cs::" in r[ik]]   # torch's kernels are the synthetic data being generated
 half = ks[len(ks) // 2:]   # second timestep (after the warm-up one)
 tot = sum(t for _, t in half)
 agg = collections.OrderedDict()
