@@ -558,9 +558,12 @@ def main():
     ap.add_argument("--gather", default="auto", choices=["auto", "fused", "ce"],
                     help="--collective peer: 'fused' = stores from the coarsening kernel itself, 'ce' = peer-to-peer DMA after "
                          "the kernel, under the next one (auto = ce: measured faster at every N, 0.988 vs 0.979 at N=2, 0.961 vs 0.940 at N=8)")
-    ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
+    ap.add_argument("--ce-streams", type=int, default=8, help="--gather ce: copy streams the peer-to-peer DMAs are spread over")
+    ap.add_argument("--collective", default="peer", choices=["peer", "nccl", "none"],
                     help="N>1: 'peer' = the coarsening kernel stores its coarse outputs into every rank's gather "
-                         "buffer over NVLink peer memory (fused all-gather); 'nccl' = asynchronous NCCL all_gather")
+                         "buffer over NVLink peer memory (fused all-gather); 'nccl' = asynchronous NCCL all_gather; "
+                         "'none' = diagnosis only: no gather at all, the max over ranks of the bare kernels (how much of the "
+                         "N-GPU loss is the spread between the GPUs of the box)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -623,7 +626,7 @@ def main():
     # destination on copy streams (no SM involved), overlapped with the next step's kernel
     use_ce = use_peer and (args.gather == "ce" or (args.gather == "auto" and world > 1))
     if use_ce:
-        ce_streams = [torch.cuda.Stream(device=dev) for _ in range(min(world, 8))]
+        ce_streams = [torch.cuda.Stream(device=dev) for _ in range(min(world, args.ce_streams))]
         locals_ = [local, torch.empty_like(local), torch.empty_like(local)]
     bar_done = [None] * nbuf  # event: the barrier that follows the kernel which wrote buffer i has completed
 
@@ -665,7 +668,7 @@ def main():
         if world > 1 and pending[i] is not None:
             pending[i].wait()  # the gather that last used this buffer pair
         outs, dco = core.pressure_coarsen(fields, delp, area, FACTOR, TOA, mask_mode="phalf", mode=mode, out=mine[i])
-        if world > 1:  # C1: collect only the small coarse outputs
+        if world > 1 and args.collective != "none":  # C1: collect only the small coarse outputs
             pending[i] = dist.all_gather_into_tensor(gathered[i], mine[i], async_op=True)
         return outs, dco
 
@@ -842,7 +845,7 @@ def main():
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "kernel": "one fused launch per step",
                    "arithmetic_mode": args.mode, "terrain": args.terrain, "l2": "inputs (1.42 GB) larger than L2, no flush needed",
-                   "per_rank": "one synthetic timestep per GPU (weak)", "collective": ("none" if world == 1 else ("peer-to-peer DMA (copy engines over NVLink, no SM) of the coarse outputs (21.8 MB/rank) into every rank's gather buffer after the kernel, under the next step's kernel; one device-side barrier per step on a side stream (three buffers)" if use_ce else "fused: the coarsening kernel stores its coarse outputs (21.8 MB/rank) into every rank's gather buffer over NVLink peer memory, one device-side barrier per step on a side stream (three buffers)") if use_peer else "NCCL all_gather of the coarse outputs (21.8 MB/rank), asynchronous: overlaps the next step")},
+                   "per_rank": "one synthetic timestep per GPU (weak)", "collective": ("none" if world == 1 else ("peer-to-peer DMA (copy engines over NVLink, no SM) of the coarse outputs (21.8 MB/rank) into every rank's gather buffer after the kernel, under the next step's kernel; one device-side barrier per step on a side stream (three buffers)" if use_ce else "fused: the coarsening kernel stores its coarse outputs (21.8 MB/rank) into every rank's gather buffer over NVLink peer memory, one device-side barrier per step on a side stream (three buffers)") if use_peer else ("NONE (diagnosis: bare kernels, not a valid multi-GPU figure)" if args.collective == "none" else "NCCL all_gather of the coarse outputs (21.8 MB/rank), asynchronous: overlaps the next step"))},
         "clocks": clocks,
         "other_mode": {"arithmetic_mode": "exact" if args.mode == "fast" else "fast", "kernel_ms": other_ms},
         "parity_slab": None if slab_err is None else {
