@@ -34,7 +34,7 @@ for fx in (2, 4, 8):
     UNITS.append((f"pc_fx{fx}_m0", "pressure_coarsen_inst.cu", ["-fmad=false", f"-DB200CS_FX={fx}", "-DB200CS_MODE=0"]))
     UNITS.append((f"pc_fx{fx}_m1", "pressure_coarsen_inst.cu", ["-fmad=true", f"-DB200CS_FX={fx}", "-DB200CS_MODE=1"]))
 
-HEADERS = ["common.cuh", "ppm_stream.cuh", "ppm_fast.cuh", "pressure_coarsen.cuh", "pressure_coarsen_fast.cuh", "pressure_coarsen_sweep.cuh", "ppm_sweep.cuh", "pressure_coarsen_tma.cuh", "pressure_coarsen_ws.cuh", "ppm_pack.cuh", os.path.join("..", "..", "include", "b200cs.h")]
+HEADERS = ["common.cuh", "ppm_stream.cuh", "ppm_fast.cuh", "pressure_coarsen.cuh", "pressure_coarsen_fast.cuh", "pressure_coarsen_sweep.cuh", "ppm_sweep.cuh", "pressure_coarsen_tma.cuh", os.path.join("experimental", "pressure_coarsen_ws.cuh"), "ppm_pack.cuh", os.path.join("..", "..", "include", "b200cs.h")]
 
 
 def _stale(target, deps):

@@ -32,10 +32,10 @@
 #pragma once
 #include <cuda.h>
 
-#include "common.cuh"
-#include "ppm_pack.cuh"
-#include "pressure_coarsen_sweep.cuh"
-#include "pressure_coarsen_tma.cuh"
+#include "../common.cuh"
+#include "../ppm_pack.cuh"
+#include "../pressure_coarsen_sweep.cuh"
+#include "../pressure_coarsen_tma.cuh"
 
 namespace b200cs {
 

@@ -83,7 +83,7 @@ B200CS_HD float xor_nsign(float a, float s) {
 }
 
 // ---- per-column geometry, shared by every field of the column (and, in the warp-specialised kernel,
-// computed by other threads than the field math: pressure_coarsen_ws.cuh) ---------------------------
+// computed by other threads than the field math: experimental/pressure_coarsen_ws.cuh) ---------------------------
 struct PpmStepGeo { float A, B, G1, G2, nG3; };
 // slope factors of layer L+1 and edge-value factors of interface L+1 from dp[L-1..L+2]
 // (mappm.f90:658-683); r01 = 1/(dp0+dp1) formed by the previous step, rn = 1/(dp1+dp2) for the next

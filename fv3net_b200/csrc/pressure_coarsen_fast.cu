@@ -6,7 +6,7 @@
 #ifdef B200CS_WITH_WS  // experimental warp-specialised kernel: developer builds only
 #include <stdlib.h>
 
-#include "pressure_coarsen_ws.cuh"
+#include "experimental/pressure_coarsen_ws.cuh"
 #endif
 
 namespace b200cs {
